@@ -1,0 +1,201 @@
+/*
+ * include/lz4e_b200.h — the C ABI between the LZ4E host library and the CUDA
+ * (sm_100a) kernels.  Plain pointers and sizes only.
+ *
+ * Three layers, lowest first:
+ *
+ *  1. DEVICE-LEVEL batch entry points (lz4e_b200_*_dev): every pointer is a
+ *     device pointer, work is enqueued on a caller stream, nothing is copied.
+ *     Blocks are described by device-side mirrors of the reference's own
+ *     types: lz4e_b200_dev_bvec mirrors struct bio_vec (doc/API.md:46-52) with
+ *     the page pointer already resolved to a device byte address, and
+ *     lz4e_b200_dev_iter mirrors struct bvec_iter (doc/API.md:72-80) plus the
+ *     index of the block's bio_vec[0] inside a shared table.  The kernels walk
+ *     these exactly like LZ4E_fillBvIterSize / LZ4E_memcpy_from_sg do
+ *     (lz4e/lz4e_compress.c:184-211, lz4e/include/lz4e_defs.h:366-402).
+ *
+ *  2. PAGE ARENAS: make a host `struct page *` resolvable on the device —
+ *     pinned host pages with a device mirror (SURVEY.md section 8b, item iv).
+ *
+ *  3. HOST-LEVEL batch entry points (lz4e_b200_*_batch): arrays of the
+ *     reference's call tuple {src, dst, srcIter, dstIter}; they translate the
+ *     bio_vecs, move pages host<->device, run layer 1 and hand back the
+ *     reference's return values.  LZ4E_compress_default (include/lz4e.h) is a
+ *     batch of one.  This is what lz4e_chunk_compress_ext
+ *     (lz4e_bdev/lz4e_chunk.c:139-159) would bind to.
+ *
+ * There is NO CPU fallback anywhere below this header.  Every function
+ * returns LZ4E_B200_OK (0) or a negative LZ4E_B200_E* code and records a
+ * message retrievable with lz4e_b200_strerror().
+ */
+#ifndef LZ4E_B200_H
+#define LZ4E_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "lz4e_bvec.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LZ4E_B200_OK 0
+#define LZ4E_B200_EIO (-5)	/* CUDA runtime/driver error */
+#define LZ4E_B200_ENOMEM (-12)
+#define LZ4E_B200_EFAULT (-14)	/* page pointer outside every registered arena */
+#define LZ4E_B200_ENODEV (-19)	/* no usable CUDA device: there is no CPU path */
+#define LZ4E_B200_EINVAL (-22)
+#define LZ4E_B200_ERANGE (-34)	/* a block broke a limit given to a *_dev call */
+
+typedef struct lz4e_b200_ctx lz4e_b200_ctx;
+typedef struct lz4e_b200_arena lz4e_b200_arena;
+
+/* ---- device-side descriptor tables -------------------------------------- */
+
+/* struct bio_vec with bv_page/bv_offset folded into a device byte address. */
+struct lz4e_b200_dev_bvec {
+	uint64_t addr; /* device address of page_address(bv_page) + bv_offset */
+	uint32_t len;  /* raw bv_len (decides the hash-table address mode) */
+	uint32_t rsvd;
+};
+
+/* struct bvec_iter for one block + where its bio_vec array starts. */
+struct lz4e_b200_dev_iter {
+	uint32_t first;	       /* index of the block's bio_vec[0] in the table */
+	uint32_t bi_size;      /* input bytes / output capacity */
+	uint32_t bi_idx;       /* as in struct bvec_iter */
+	uint32_t bi_bvec_done; /* as in struct bvec_iter (mid-bvec start) */
+};
+
+/* Linear positions at which the reference leaves *srcIter / *dstIter
+ * (lz4e/lz4e_compress.c:304-305, :528-529). */
+struct lz4e_b200_dev_end {
+	uint32_t src_pos;
+	uint32_t dst_pos;
+};
+
+/* ---- context ------------------------------------------------------------- */
+int lz4e_b200_device_count(void);
+int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out);
+void lz4e_b200_ctx_destroy(lz4e_b200_ctx *ctx);
+/* process-wide default context on $LZ4E_B200_DEVICE (default 0); NULL and a
+ * message on stderr when no device is usable */
+lz4e_b200_ctx *lz4e_b200_default_ctx(void);
+const char *lz4e_b200_strerror(lz4e_b200_ctx *ctx);
+int lz4e_b200_ctx_device(lz4e_b200_ctx *ctx);
+int lz4e_b200_ctx_sm_count(lz4e_b200_ctx *ctx);
+/* kernels launched by this context so far (bench.py's gpu_launches) */
+uint64_t lz4e_b200_kernel_launches(lz4e_b200_ctx *ctx);
+/* wait for `stream` (NULL = the context's own stream) and report device-side
+ * faults raised by earlier *_dev calls (LZ4E_B200_ERANGE ...) */
+int lz4e_b200_sync(lz4e_b200_ctx *ctx, void *stream);
+
+/* ---- layer 1: device-level batches --------------------------------------- */
+
+/*
+ * LZ4E_compress_default for `nblocks` independent blocks.
+ *  src_bvecs/src_iters   source tables (device memory)
+ *  dst_bvecs/dst_iters   destination tables; dst_iters[b].bi_size = capacity
+ *  max_in_bytes          upper bound of src_iters[].bi_size (sizes the shared
+ *                        memory staging; a larger block raises ERANGE)
+ *  rets[b]               bytes written, or 0 exactly where the reference
+ *                        returns 0
+ *  ends[b]               optional (may be NULL) iterator end state
+ * Output bytes are identical to the reference's for the same source bytes and
+ * source segmentation; nothing beyond rets[b] bytes of a destination is
+ * written.
+ */
+int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
+			   const struct lz4e_b200_dev_bvec *src_bvecs,
+			   const struct lz4e_b200_dev_iter *src_iters,
+			   const struct lz4e_b200_dev_bvec *dst_bvecs,
+			   const struct lz4e_b200_dev_iter *dst_iters,
+			   uint32_t nblocks, uint32_t max_in_bytes,
+			   int32_t *rets, struct lz4e_b200_dev_end *ends);
+
+/*
+ * LZ4E decompression (lz4e/lz4e_decompress.c:462-470 semantics on the
+ * linearised bytes) with scatter-gather source and destination.
+ *  src_iters[b].bi_size  compressed size,  dst_iters[b].bi_size  capacity
+ *  rets[b]               decoded bytes, or the reference's negative error
+ */
+int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
+			     const struct lz4e_b200_dev_bvec *src_bvecs,
+			     const struct lz4e_b200_dev_iter *src_iters,
+			     const struct lz4e_b200_dev_bvec *dst_bvecs,
+			     const struct lz4e_b200_dev_iter *dst_iters,
+			     uint32_t nblocks, uint32_t max_in_bytes,
+			     uint32_t max_out_bytes, int32_t *rets);
+
+/*
+ * Compacted-output compression (SURVEY.md section 8b, item iii): all blocks
+ * are written back to back into ONE destination stream described by
+ * dst_bvecs/dst_stream.  Blocks are compressed into context scratch, a device
+ * prefix scan over rets[] yields offsets[b] (exclusive, nblocks+1 entries)
+ * and a scatter kernel packs them.  A block that fails (ret 0) takes no space.
+ * Capacity per block is LZ4E_COMPRESSBOUND (noLimit mode).
+ */
+int lz4e_b200_compress_compact_dev(lz4e_b200_ctx *ctx, void *stream,
+				   const struct lz4e_b200_dev_bvec *src_bvecs,
+				   const struct lz4e_b200_dev_iter *src_iters,
+				   const struct lz4e_b200_dev_bvec *dst_bvecs,
+				   const struct lz4e_b200_dev_iter *dst_stream,
+				   uint32_t nblocks, uint32_t max_in_bytes,
+				   int32_t *rets, uint64_t *offsets);
+
+/* Fill SG blocks with the synthetic benchmark contents of
+ * lz4-sgori_b200/csrc/lz4e_synth.h: class = (first_index + b) & 3, seed =
+ * first_index + b. */
+int lz4e_b200_synth_fill_dev(lz4e_b200_ctx *ctx, void *stream,
+			     const struct lz4e_b200_dev_bvec *bvecs,
+			     const struct lz4e_b200_dev_iter *iters,
+			     uint32_t nblocks, uint32_t first_index);
+/* the same generator on the host */
+void lz4e_b200_synth_fill_host(uint8_t *buf, uint32_t n, uint32_t cls,
+			       uint32_t seed);
+
+/* ---- layer 2: page arenas ------------------------------------------------ */
+int lz4e_b200_arena_create(lz4e_b200_ctx *ctx, size_t npages,
+			   lz4e_b200_arena **out);
+void lz4e_b200_arena_destroy(lz4e_b200_arena *arena);
+struct page *lz4e_b200_arena_pages(lz4e_b200_arena *arena); /* pinned host */
+void *lz4e_b200_arena_dev_base(lz4e_b200_arena *arena);	    /* device mirror */
+size_t lz4e_b200_arena_npages(lz4e_b200_arena *arena);
+int lz4e_b200_arena_upload(lz4e_b200_arena *arena, size_t first_page,
+			   size_t npages);
+int lz4e_b200_arena_download(lz4e_b200_arena *arena, size_t first_page,
+			     size_t npages);
+
+/* ---- layer 3: host-level batches ----------------------------------------- */
+
+/* One LZ4E call: the reference's argument tuple plus the return slot. */
+struct lz4e_b200_req {
+	const struct bio_vec *src;
+	struct bio_vec *dst;
+	struct bvec_iter *src_iter;
+	struct bvec_iter *dst_iter;
+	int ret;
+	int rsvd;
+};
+
+#define LZ4E_B200_F_SRC_RESIDENT 1u /* source pages already current on device */
+#define LZ4E_B200_F_DST_ON_DEVICE 2u /* leave results in the device mirror */
+#define LZ4E_B200_F_KEEP_ITERS 4u   /* do not move the iterators */
+
+/* Pages may live in an arena (fast path: one bulk copy per arena per
+ * direction) or anywhere in host memory (bounced segment by segment). */
+int lz4e_b200_compress_batch(lz4e_b200_ctx *ctx, struct lz4e_b200_req *reqs,
+			     size_t n, unsigned flags);
+int lz4e_b200_decompress_batch(lz4e_b200_ctx *ctx, struct lz4e_b200_req *reqs,
+			       size_t n, unsigned flags);
+
+/* Contiguous range [first, first+count) of block indices owned by `rank`
+ * out of `world` (shard by block index, no collective). */
+void lz4e_b200_shard_range(uint64_t nblocks, uint32_t rank, uint32_t world,
+			   uint64_t *first, uint64_t *count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LZ4E_B200_H */

@@ -1,0 +1,486 @@
+/*
+ * lz4e_compress_body.cuh — one warp compresses one block.
+ *
+ * What it must reproduce, byte for byte: LZ4E_compress_generic
+ * (lz4e/lz4e_compress.c:218-534 of the reference) as instantiated by
+ * LZ4E_compress_default (:536-569): greedy LZ4 "fast", acceleration 1, noDict,
+ * hash-table address mode chosen from the SOURCE SEGMENTATION by
+ * LZ4E_fillBvIterSize (:184-211).
+ *
+ * How it is done here (none of this is in the reference):
+ *
+ *  - The block is gathered once from its SG segments into shared memory as a
+ *    linear byte string (lz4e_copy.cuh), so the per-access bio_vec walk of
+ *    lz4e_defs.h:366-402 disappears from the hot loop.
+ *  - The hash table lives in shared memory, same number of entries as the
+ *    reference (8192 / 4096 / 2048 for byU16 / byU32 / byU64,
+ *    lz4e_compress.c:48-57) but holding 16-bit LINEAR positions: the
+ *    reference's (bvec index, offset) address (lz4e_defs.h:641-686) is a
+ *    bijection on positions and "raw == 0" means position 0 in both.
+ *  - The reference's search loop (:292-336) visits positions p_0, p_1, ... with
+ *    a fixed step schedule and, at each one, reads table[h], writes table[h]
+ *    and compares 4 bytes.  A visit that does not match changes nothing but
+ *    the table.  So 32 consecutive visits are evaluated SPECULATIVELY by the 32
+ *    lanes; __match_any_sync resolves visits of one batch that hit the same
+ *    table slot (a later visit must see the earlier visit's position), the
+ *    first matching lane wins, and only visits up to and including the winner
+ *    are committed to the table — exactly the serial order.
+ *  - The two extra table operations after every match ("fill table" at ip-2,
+ *    :461-464, and "test next position" at ip, :467-493) are lanes -2 and -1 of
+ *    the next batch.
+ *  - Catch-up (:339-349) and LZ4E_count (lz4e_defs.h:587-636) are
+ *    ballot/ffs reductions over per-lane compares.
+ *  - A sequence is emitted only when literal length AND match length are
+ *    known, so the output is append-only; it is staged in shared memory and
+ *    flushed to the destination SG segments in coalesced pieces.
+ */
+#ifndef LZ4E_COMPRESS_BODY_CUH
+#define LZ4E_COMPRESS_BODY_CUH
+
+#include "../../include/lz4e_b200.h"
+#include "lz4e_copy.cuh"
+#include "lz4e_simt.h"
+
+#define LZ4E_K_MAX_INPUT 0x7E000000u /* lz4e.h:24 */
+#define LZ4E_K_TABLE_BYTES 16384u    /* LZ4E_MEMORY_USAGE 14, lz4e.h:11 */
+#define LZ4E_K_PAD 48u		     /* slack after each staging area */
+
+#define LZ4E_FAULT_RANGE 1u /* a block exceeded the limits given at launch */
+
+enum { LZ4E_TT_U16 = 1, LZ4E_TT_U32 = 3, LZ4E_TT_U64 = 7 }; /* lz4e_defs.h:689 */
+
+struct lz4e_compress_args {
+	const struct lz4e_b200_dev_bvec *src_bvecs;
+	const struct lz4e_b200_dev_iter *src_iters;
+	const struct lz4e_b200_dev_bvec *dst_bvecs;
+	const struct lz4e_b200_dev_iter *dst_iters;
+	int32_t *rets;
+	struct lz4e_b200_dev_end *ends; /* may be NULL */
+	uint32_t *work_counter;		/* zeroed before launch */
+	uint32_t *faults;
+	uint32_t nblocks;
+	uint32_t in_cap;  /* bytes of input staging (multiple of 16) */
+	uint32_t out_cap; /* bytes of output staging (multiple of 16, >= 1024) */
+};
+
+/* shared memory needed by one warp */
+static inline uint32_t lz4e_compress_smem_bytes(uint32_t in_cap, uint32_t out_cap)
+{
+	return LZ4E_K_TABLE_BYTES + in_cap + LZ4E_K_PAD + out_cap + LZ4E_K_PAD;
+}
+
+/* number of bytes advanced after k search visits: visit k uses step 1 for
+ * k == 0 and (63 + k) >> 6 afterwards (searchMatchNb++ >> LZ4_SKIPTRIGGER,
+ * lz4e_compress.c:296-306) */
+LZ4E_DEV uint32_t lz4e_search_advance(int k)
+{
+	if (k <= 65)
+		return (uint32_t)k;
+	const uint32_t a1 = 63u + (uint32_t)k; /* A + 1 with A = 62 + k */
+	const uint32_t q = a1 >> 6;
+
+	return 1u + 32u * q * (q - 1u) + (a1 - 64u * q) * q;
+}
+
+/* hash of the bytes at a position, lz4e_compress.c:59-96; w0/w1 are the two
+ * aligned words around the position, sh its bit offset in w0 */
+LZ4E_DEV uint32_t lz4e_hash(uint32_t seq, uint32_t byte4, int tt)
+{
+	if (tt == LZ4E_TT_U32) {
+		const uint64_t v = (uint64_t)seq | ((uint64_t)byte4 << 32);
+
+		return (uint32_t)(((v << 24) * 889523592379ULL) >> 52);
+	}
+	return (seq * 2654435761U) >> (tt == LZ4E_TT_U16 ? 19 : 21);
+}
+
+struct lz4e_out_stage {
+	uint8_t *base;	    /* staging area (shared memory) */
+	uint8_t *cur0;	    /* address holding output byte `win` */
+	uint32_t win;	    /* linear output position of cur0 */
+	uint32_t cap;	    /* usable bytes behind cur0 */
+	lz4e_cursor dst;    /* where output byte `win` goes */
+};
+
+LZ4E_DEV void lz4e_stage_rebase(lz4e_out_stage &s, uint32_t op, uint32_t out_cap)
+{
+	/* keep staging and destination congruent mod 16 so the flush is vector
+	 * stores */
+	const uint32_t shift = (uint32_t)(s.dst.v->addr + s.dst.done) & 15u;
+
+	s.cur0 = s.base + shift;
+	s.win = op;
+	s.cap = out_cap;
+}
+
+LZ4E_DEV void lz4e_stage_flush(lz4e_out_stage &s, uint32_t op, uint32_t out_cap,
+			       uint32_t lane)
+{
+	lz4e_syncwarp(LZ4E_FULL);
+	lz4e_scatter<32>(s.dst, s.cur0, op - s.win, lane);
+	lz4e_syncwarp(LZ4E_FULL);
+	lz4e_stage_rebase(s, op, out_cap);
+}
+
+/* length bytes of a run >= 15: (run - 15) / 255 bytes of 255, then the rest */
+LZ4E_DEV void lz4e_put_run(uint8_t *p, uint32_t count, uint32_t last,
+			   uint32_t lane)
+{
+	for (uint32_t i = lane; i < count; i += 32)
+		p[i] = (i + 1 == count) ? (uint8_t)last : (uint8_t)255;
+}
+
+/*
+ * Compress block b.  sm points at this warp's shared memory
+ * (lz4e_compress_smem_bytes()).  All 32 lanes call it together.
+ */
+LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
+				  uint8_t *sm, uint32_t lane)
+{
+	const struct lz4e_b200_dev_iter si = a.src_iters[b];
+	const struct lz4e_b200_dev_iter di = a.dst_iters[b];
+	const uint32_t n = si.bi_size;
+	const uint32_t cap = di.bi_size;
+	uint16_t *tab = reinterpret_cast<uint16_t *>(sm);
+	uint8_t *in_area = sm + LZ4E_K_TABLE_BYTES;
+	uint8_t *out_area = in_area + a.in_cap + LZ4E_K_PAD;
+	const uint8_t *d; /* d[pos] = source byte at linear position pos */
+	int tt = LZ4E_TT_U16;
+	int32_t ret = 0;
+	uint32_t src_end = 0, dst_end = 0;
+
+	if (n > LZ4E_K_MAX_INPUT) /* lz4e_compress.c:245-248 */
+		goto done;
+	if (n > a.in_cap || n > 65536u) {
+		if (lane == 0)
+			lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
+		goto done;
+	}
+
+	/* ---- gather + address mode (lz4e_compress.c:184-211) ---- */
+	{
+		const struct lz4e_b200_dev_bvec *v =
+			a.src_bvecs + si.first + si.bi_idx;
+		uint32_t done_in = si.bi_bvec_done, rem = n, pos = 0, i = 0;
+		bool too_many = false;
+		uint8_t *dbase = in_area;
+
+		if (n)
+			dbase += (uint32_t)(v->addr + done_in) & 15u;
+		d = dbase;
+		while (rem) {
+			if (i >= BIO_MAX_VECS) {
+				too_many = true;
+				break;
+			}
+			const uint32_t len = v[i].len;
+			uint32_t take = len - done_in;
+			uint8_t *g = (uint8_t *)(uintptr_t)(v[i].addr + done_in);
+
+			LZ4E_ASSUME_GLOBAL(g);
+			if (i >= 16 || len > 4096u)
+				tt |= LZ4E_TT_U32;
+			if (len > (1u << 24))
+				tt |= LZ4E_TT_U64;
+			if (take > rem)
+				take = rem;
+			lz4e_copy<32>(dbase + pos, g, take, lane);
+			pos += take;
+			rem -= take;
+			done_in = 0;
+			i++;
+		}
+		if (too_many && n >= 13) /* :268-277 */
+			goto done;
+		lz4e_syncwarp(LZ4E_FULL); /* gathered bytes visible to all lanes */
+	}
+
+	{
+		const bool limited = cap < n + n / 255u + 16u; /* :553 */
+		const uint32_t mflimit = n - 12u;
+		const uint32_t matchlimit = n - 5u;
+		uint32_t anchor = 0, op = 0;
+		lz4e_out_stage st;
+
+		st.base = out_area;
+		st.dst = lz4e_cursor_init(a.dst_bvecs, di);
+		if (cap)
+			lz4e_stage_rebase(st, 0, a.out_cap);
+		else
+			st.cur0 = out_area, st.win = 0, st.cap = a.out_cap;
+
+		if (n >= 13) {
+			/* zero the table: (1 << hashLog) 16-bit entries */
+			const uint32_t tbytes = tt == LZ4E_TT_U16   ? 16384u
+						: tt == LZ4E_TT_U32 ? 8192u
+								    : 4096u;
+			const lz4e_u128 z = { 0, 0, 0, 0 };
+
+			for (uint32_t i = lane * 16u; i < tbytes; i += 512u)
+				lz4e_st128(sm + i, z);
+			lz4e_syncwarp(LZ4E_FULL); /* table + gathered input visible */
+
+			/* first byte (:280-282): table[hash(0)] = 0 is a no-op on a
+			 * zeroed table of positions; search starts at 1 */
+			uint32_t p0 = 1;
+			int kbase = 0;
+
+			src_end = 1;
+			for (;;) {
+				/* ---- one speculative batch of 32 visits ---- */
+				const int k = kbase + (int)lane;
+				uint32_t pos, seq = 0, h = 0xffffffffu, m = 0;
+				bool valid, ins_only = false;
+
+				if (k == -2) {
+					pos = p0 - 3u; /* fill table at ip-2 */
+					valid = true;
+					ins_only = true;
+				} else if (k == -1) {
+					pos = p0 - 1u; /* test next position */
+					valid = true;
+				} else {
+					const uint32_t step =
+						k == 0 ? 1u : (63u + (uint32_t)k) >> 6;
+
+					pos = p0 + lz4e_search_advance(k);
+					valid = pos + step <= mflimit;
+				}
+				if (valid) {
+					const uintptr_t ad = (uintptr_t)(d + pos);
+					const uint8_t *al =
+						(const uint8_t *)(ad & ~(uintptr_t)3);
+					const uint32_t sh = (uint32_t)(ad & 3) * 8u;
+					const uint32_t w0 = lz4e_ld32a(al);
+					const uint32_t w1 = lz4e_ld32a(al + 4);
+
+					seq = lz4e_funnel_r(w0, w1, sh);
+					h = lz4e_hash(seq, (w1 >> sh) & 0xffu, tt);
+					m = tab[h];
+				}
+				{
+					const uint32_t peers = lz4e_match_any(LZ4E_FULL, h);
+					const uint32_t lower = peers & ((1u << lane) - 1u);
+					const int srcl = lower ? 31 - lz4e_clz(lower)
+							       : (int)lane;
+					const uint32_t mj = lz4e_shfl(LZ4E_FULL, pos, srcl);
+					bool ok = false;
+
+					if (lower)
+						m = mj;
+					if (valid && !ins_only && m + 65535u >= pos)
+						ok = lz4e_ld32u(d + m) == seq;
+
+					const uint32_t okmask = lz4e_ballot(LZ4E_FULL, ok);
+					const uint32_t vmask = lz4e_ballot(LZ4E_FULL, valid);
+
+					if (okmask == 0) {
+						if (vmask != LZ4E_FULL) {
+							/* ran into mflimit: last literals.
+							 * *srcIter stays at the last
+							 * visited search position */
+							const int nv = lz4e_popc(vmask);
+							const int lastk = kbase + nv - 1;
+
+							if (lastk >= 0)
+								src_end = p0 +
+									lz4e_search_advance(lastk);
+							else
+								src_end = p0;
+							break;
+						}
+						/* commit all 32 visits, keep searching */
+						if ((peers >> lane) >> 1 == 0)
+							tab[h] = (uint16_t)pos;
+						lz4e_syncwarp(LZ4E_FULL);
+						kbase += 32;
+						continue;
+					}
+
+					/* ---- a match: commit visits 0..f in order ---- */
+					const int f = lz4e_ffs(okmask) - 1;
+					const uint32_t upto = (2u << f) - 1u;
+					const uint32_t later =
+						peers & upto & ~((2u << lane) - 1u);
+
+					if ((int)lane <= f && later == 0)
+						tab[h] = (uint16_t)pos;
+
+					uint32_t ip = lz4e_shfl(LZ4E_FULL, pos, f);
+					uint32_t mp = lz4e_shfl(LZ4E_FULL, m, f);
+
+					/* ---- catch up (:339-349) ---- */
+					uint32_t back = 0;
+					{
+						uint32_t lim = ip - anchor;
+
+						if (mp < lim)
+							lim = mp;
+						while (back < lim) {
+							const uint32_t i = back + lane;
+							bool eq = false;
+
+							if (i < lim)
+								eq = d[ip - 1u - i] ==
+								     d[mp - 1u - i];
+							const uint32_t ne =
+								lz4e_ballot(LZ4E_FULL, !eq);
+							if (ne) {
+								back += (uint32_t)lz4e_ffs(ne) - 1u;
+								break;
+							}
+							back += 32u;
+						}
+					}
+					/* ---- match length (lz4e_defs.h:587-636) ---- */
+					uint32_t ml = 0;
+					{
+						const uint32_t fip = ip + 4u, fm = mp + 4u;
+						const uint32_t limit = matchlimit - fip;
+
+						for (;;) {
+							const uint32_t o = ml + 4u * lane;
+							uint32_t x = 1;
+
+							if (o < limit)
+								x = lz4e_ld32u(d + fip + o) ^
+								    lz4e_ld32u(d + fm + o);
+							const uint32_t nz =
+								lz4e_ballot(LZ4E_FULL, x != 0);
+							if (nz) {
+								const int fl = lz4e_ffs(nz) - 1;
+								const uint32_t xf =
+									lz4e_shfl(LZ4E_FULL, x, fl);
+								ml += 4u * (uint32_t)fl +
+								      (((uint32_t)lz4e_ffs(xf) - 1u) >> 3);
+								break;
+							}
+							ml += 128u;
+						}
+						if (ml > limit)
+							ml = limit;
+					}
+
+					/* ---- emit one sequence (:352-450) ---- */
+					{
+						const uint32_t lit = ip - back - anchor;
+						const uint32_t mc = back + ml;
+						const uint32_t off = ip - mp;
+						const uint32_t lit_ext =
+							lit >= 15u ? (lit - 15u) / 255u + 1u : 0u;
+						const uint32_t mc_ext =
+							mc >= 15u ? (mc - 15u) / 255u + 1u : 0u;
+						const uint32_t need =
+							1u + lit_ext + lit + 2u + mc_ext;
+
+						if (limited &&
+						    (op + 1u + lit + 8u + lit / 255u > cap ||
+						     op + 1u + lit_ext + lit + 2u + 6u + (mc >> 8) >
+							     cap))
+							goto done; /* ret stays 0 */
+
+						if (op - st.win + need > st.cap)
+							lz4e_stage_flush(st, op, a.out_cap, lane);
+						const bool stream = op - st.win + need > st.cap;
+						uint8_t *o = st.cur0 + (op - st.win);
+
+						if (lane == 0)
+							o[0] = (uint8_t)(((lit < 15u ? lit : 15u) << 4) |
+									 (mc < 15u ? mc : 15u));
+						lz4e_put_run(o + 1, lit_ext, (lit - 15u) % 255u, lane);
+						o += 1u + lit_ext;
+						op += 1u + lit_ext;
+						if (stream) {
+							/* literal run larger than the staging
+							 * area: flush the header, then stream
+							 * the literals straight from the
+							 * gathered input */
+							lz4e_stage_flush(st, op, a.out_cap, lane);
+							lz4e_scatter<32>(st.dst, d + anchor, lit, lane);
+							op += lit;
+							lz4e_stage_rebase(st, op, a.out_cap);
+							o = st.cur0;
+						} else {
+							lz4e_copy<32>(o, d + anchor, lit, lane);
+							o += lit;
+							op += lit;
+						}
+						if (lane == 0) {
+							o[0] = (uint8_t)off;
+							o[1] = (uint8_t)(off >> 8);
+						}
+						lz4e_put_run(o + 2, mc_ext, (mc - 15u) % 255u, lane);
+						op += 2u + mc_ext;
+					}
+
+					anchor = ip + 4u + ml;
+					if (anchor > mflimit) { /* :456 */
+						src_end = anchor;
+						break;
+					}
+					p0 = anchor + 1u;
+					kbase = -2;
+					lz4e_syncwarp(LZ4E_FULL); /* table writes visible */
+				}
+			}
+		}
+
+		/* ---- last literals (:500-530) ---- */
+		{
+			const uint32_t run = n - anchor;
+			const uint32_t ext = run >= 15u ? (run - 15u) / 255u + 1u : 0u;
+
+			if (limited && op + run + 1u + (run + 240u) / 255u > cap)
+				goto done;
+			if (op - st.win + 1u + ext > st.cap)
+				lz4e_stage_flush(st, op, a.out_cap, lane);
+			uint8_t *o = st.cur0 + (op - st.win);
+
+			if (lane == 0)
+				o[0] = (uint8_t)((run < 15u ? run : 15u) << 4);
+			lz4e_put_run(o + 1, ext, (run - 15u) % 255u, lane);
+			op += 1u + ext;
+			dst_end = op;
+			if (op - st.win + run > st.cap) {
+				lz4e_stage_flush(st, op, a.out_cap, lane);
+				lz4e_scatter<32>(st.dst, d + anchor, run, lane);
+				op += run;
+			} else {
+				lz4e_copy<32>(o + 1u + ext, d + anchor, run, lane);
+				op += run;
+				lz4e_syncwarp(LZ4E_FULL);
+				lz4e_scatter<32>(st.dst, st.cur0, op - st.win, lane);
+			}
+			ret = (int32_t)op;
+		}
+	}
+
+done:
+	if (lane == 0) {
+		a.rets[b] = ret;
+		if (a.ends) {
+			a.ends[b].src_pos = ret ? src_end : 0;
+			a.ends[b].dst_pos = ret ? dst_end : 0;
+		}
+	}
+	/* the next block reuses this warp's shared memory */
+	lz4e_syncwarp(LZ4E_FULL);
+}
+
+/* persistent loop: warps pull block indices from a global counter */
+LZ4E_DEV void lz4e_compress_warp(const lz4e_compress_args &a, uint8_t *sm,
+				 uint32_t lane)
+{
+	for (;;) {
+		uint32_t b = 0;
+
+		if (lane == 0)
+			b = lz4e_atomic_add(a.work_counter, 1u);
+		b = lz4e_shfl(LZ4E_FULL, b, 0);
+		if (b >= a.nblocks)
+			break;
+		lz4e_compress_block(a, b, sm, lane);
+	}
+}
+
+#endif /* LZ4E_COMPRESS_BODY_CUH */

@@ -1,0 +1,355 @@
+/*
+ * lz4e_decompress_body.cuh — a group of GS lanes (GS = 8, 16 or 32) decodes
+ * one LZ4 block; 32/GS blocks are in flight per warp.
+ *
+ * Semantics: LZ4E_decompress_safe (lz4e/lz4e_decompress.c:462-470 of the
+ * reference), i.e. LZ4E_decompress_generic (:62-460) with endOnInputSize,
+ * decode_full_block, noDict, lowPrefix == dest — including which malformed
+ * inputs are rejected and the value returned for them, -(input offset) - 1
+ * (:458-459).  The reference function takes contiguous buffers; here source and
+ * destination are scatter-gather lists (the SG decoder north_star asks for).
+ *
+ * Control flow is uniform inside a group: every lane parses the same token,
+ * lengths and offset (broadcast loads), then lanes split the literal and match
+ * bytes between them.  The two-stage "shortcut" of :150-191 is kept only as
+ * the predicate that decides which end-of-block checks apply, because that is
+ * observable in the return value for malformed streams.
+ *
+ * Overlapping matches (offset < match length) are resolved arithmetically:
+ * out[op + i] = out[op - offset + i % offset] reads only bytes that were final
+ * before the match started, so all lanes can copy at once (the
+ * replicated-pattern path).  offset == 0 yields zero bytes, exactly what
+ * LZ4_write32(op, offset) at :309-314 makes the reference produce.
+ *
+ * STAGE = true : the block's output is built in shared memory and written to
+ *                the destination segments once, coalesced (blocks up to
+ *                stage_cap bytes, e.g. the 4 KiB chunk size of lz4e_bdev).
+ * STAGE = false: output goes straight to global memory; if the destination is
+ *                one contiguous segment it is used in place, otherwise the
+ *                block is decoded into a per-group scratch slot and scattered.
+ */
+#ifndef LZ4E_DECOMPRESS_BODY_CUH
+#define LZ4E_DECOMPRESS_BODY_CUH
+
+#include "../../include/lz4e_b200.h"
+#include "lz4e_copy.cuh"
+#include "lz4e_simt.h"
+
+#define LZ4E_D_PAD 32u
+#ifndef LZ4E_FAULT_RANGE
+#define LZ4E_FAULT_RANGE 1u
+#endif
+
+struct lz4e_decompress_args {
+	const struct lz4e_b200_dev_bvec *src_bvecs;
+	const struct lz4e_b200_dev_iter *src_iters;
+	const struct lz4e_b200_dev_bvec *dst_bvecs;
+	const struct lz4e_b200_dev_iter *dst_iters;
+	int32_t *rets;
+	uint32_t *work_counter;
+	uint32_t *faults;
+	uint32_t nblocks;
+	uint32_t stage_cap;	 /* STAGE: shared-memory bytes per group */
+	uint8_t *scratch;	 /* !STAGE: linear slots for non-contiguous dst */
+	uint32_t scratch_stride; /* bytes per slot */
+};
+
+/* forward-only view of the compressed SG stream: byte p lives at bias[p]
+ * while lo <= p < hi */
+struct lz4e_in_view {
+	const uint8_t *bias;
+	const struct lz4e_b200_dev_bvec *v;
+	uint32_t hi;
+	uint32_t end; /* compressed size */
+};
+
+LZ4E_DEV void lz4e_in_open(lz4e_in_view &in,
+			   const struct lz4e_b200_dev_bvec *table,
+			   const struct lz4e_b200_dev_iter &it)
+{
+	in.v = table + it.first + it.bi_idx;
+	in.end = it.bi_size;
+	if (it.bi_size == 0) {
+		in.hi = 0;
+		in.bias = 0;
+		return;
+	}
+	const uint32_t room = in.v->len - it.bi_bvec_done;
+
+	in.hi = room < it.bi_size ? room : it.bi_size;
+	in.bias = (const uint8_t *)(uintptr_t)(in.v->addr + it.bi_bvec_done);
+	LZ4E_ASSUME_GLOBAL(in.bias);
+}
+
+/* make the segment holding position p current (p < end) */
+LZ4E_DEV void lz4e_in_seek(lz4e_in_view &in, uint32_t p)
+{
+	while (p >= in.hi && in.hi < in.end) {
+		const uint32_t lo = in.hi;
+
+		in.v++;
+		in.hi = lo + in.v->len;
+		if (in.hi > in.end || in.hi < lo)
+			in.hi = in.end;
+		in.bias = (const uint8_t *)(uintptr_t)(in.v->addr - lo);
+		LZ4E_ASSUME_GLOBAL(in.bias);
+	}
+}
+
+LZ4E_DEV uint32_t lz4e_in_rd8_slow(const lz4e_in_view &in, uint32_t p)
+{
+	const struct lz4e_b200_dev_bvec *w = in.v + 1;
+	uint32_t base = in.hi;
+
+	for (;;) {
+		if (p - base < w->len) {
+			const uint8_t *g =
+				(const uint8_t *)(uintptr_t)(w->addr + (p - base));
+			LZ4E_ASSUME_GLOBAL(g);
+			return *g;
+		}
+		base += w->len;
+		w++;
+	}
+}
+
+LZ4E_DEV uint32_t lz4e_in_rd8(const lz4e_in_view &in, uint32_t p)
+{
+	if (p < in.hi)
+		return in.bias[p];
+	return lz4e_in_rd8_slow(in, p);
+}
+
+template <int GS, bool STAGE>
+struct lz4e_dgroup {
+	lz4e_in_view in;
+	uint8_t *out;	/* out[op]: linear output (shared or global) */
+	uint32_t b;	/* block index */
+	int32_t iend;	/* compressed size */
+	int32_t oend;	/* output capacity */
+	uint32_t ip, op;
+	bool active;	/* a block is being decoded */
+	bool scatter;	/* !STAGE: output sits in scratch, scatter when done */
+};
+
+/* write the result of a finished block and move its bytes home */
+template <int GS, bool STAGE>
+LZ4E_DEV void lz4e_dgroup_finish(const lz4e_decompress_args &a,
+				 lz4e_dgroup<GS, STAGE> &g, int32_t ret,
+				 uint32_t gmask, uint32_t gl)
+{
+	lz4e_syncwarp(gmask);
+	if ((STAGE || g.scatter) && ret > 0) {
+		lz4e_cursor c = lz4e_cursor_init(a.dst_bvecs, a.dst_iters[g.b]);
+
+		lz4e_scatter<GS>(c, g.out, (uint32_t)ret, gl);
+	}
+	if (gl == 0)
+		a.rets[g.b] = ret;
+	g.active = false;
+	lz4e_syncwarp(gmask); /* staging is reused by the next block */
+}
+
+/*
+ * sm: this warp's shared memory ((32/GS) * (stage_cap + LZ4E_D_PAD) bytes when
+ * STAGE, unused otherwise); slot0: index of this warp's first scratch slot.
+ */
+template <int GS, bool STAGE>
+LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
+					uint8_t *sm, uint32_t slot0,
+					uint32_t lane)
+{
+	const uint32_t gl = lane & (GS - 1);  /* lane inside the group */
+	const uint32_t gi = lane / GS;	      /* group inside the warp */
+	const uint32_t gmask =
+		(GS == 32 ? 0xffffffffu : ((1u << GS) - 1u)) << (gi * GS);
+	const int gleader = (int)(gi * GS);
+	lz4e_dgroup<GS, STAGE> g;
+
+	g.active = false;
+	g.scatter = false;
+	for (;;) {
+		if (!g.active) {
+			/* ---- next block for this group ---- */
+			uint32_t b = 0;
+
+			if (gl == 0)
+				b = lz4e_atomic_add(a.work_counter, 1u);
+			b = lz4e_shfl(gmask, b, gleader);
+			if (b >= a.nblocks)
+				break;
+			const struct lz4e_b200_dev_iter si = a.src_iters[b];
+			const struct lz4e_b200_dev_iter di = a.dst_iters[b];
+
+			g.b = b;
+			g.iend = (int32_t)si.bi_size;
+			g.oend = (int32_t)di.bi_size;
+			g.ip = g.op = 0;
+			g.active = true;
+			g.scatter = false;
+			if (si.bi_size > (16u << 20) || di.bi_size > 0x7fffffffu ||
+			    (STAGE && di.bi_size > a.stage_cap)) {
+				if (gl == 0) {
+					lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
+					a.rets[b] = -1;
+				}
+				g.active = false;
+				continue;
+			}
+			/* special cases, lz4e_decompress.c:113-120 */
+			if (g.oend == 0 || g.iend == 0) {
+				int32_t r = -1;
+
+				lz4e_in_open(g.in, a.src_bvecs, si);
+				if (g.oend == 0 && g.iend == 1 &&
+				    lz4e_in_rd8(g.in, 0) == 0)
+					r = 0;
+				if (gl == 0)
+					a.rets[b] = r;
+				g.active = false;
+				continue;
+			}
+			lz4e_in_open(g.in, a.src_bvecs, si);
+			const struct lz4e_b200_dev_bvec *dv =
+				a.dst_bvecs + di.first + di.bi_idx;
+
+			if (STAGE) {
+				/* congruent mod 16 with the first destination
+				 * segment, so the final scatter is vector stores */
+				g.out = sm + gi * (a.stage_cap + LZ4E_D_PAD) +
+					((uint32_t)(dv->addr + di.bi_bvec_done) & 15u);
+			} else {
+
+				if (dv->len - di.bi_bvec_done >= di.bi_size) {
+					g.out = (uint8_t *)(uintptr_t)(dv->addr +
+								       di.bi_bvec_done);
+				} else {
+					if (di.bi_size > a.scratch_stride) {
+						if (gl == 0) {
+							lz4e_atomic_or(a.faults,
+								       LZ4E_FAULT_RANGE);
+							a.rets[b] = -1;
+						}
+						g.active = false;
+						continue;
+					}
+					g.out = a.scratch + (size_t)(slot0 + gi) *
+								    a.scratch_stride;
+					g.scatter = true;
+				}
+				LZ4E_ASSUME_GLOBAL(g.out);
+			}
+		}
+
+		/* ---- one sequence ---- */
+		const int32_t iend = g.iend, oend = g.oend;
+		uint32_t ip = g.ip, op = g.op;
+
+		lz4e_in_seek(g.in, ip);
+		const uint32_t token = lz4e_in_rd8(g.in, ip++);
+		uint32_t len = token >> 4;
+		const bool shortcut = len != 15u && (int32_t)ip < iend - 16 &&
+				      (int32_t)op <= oend - 32; /* :150-156 */
+
+		if (!shortcut) {
+			if (len == 15u) { /* :194-220 */
+				uint32_t s;
+
+				if ((int32_t)ip >= iend - 15) {
+					lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
+					continue;
+				}
+				do {
+					s = lz4e_in_rd8(g.in, ip++);
+					len += s;
+				} while ((int32_t)ip < iend - 15 && s == 255u);
+			}
+			/* :222-266 */
+			if ((int64_t)op + len > (int64_t)oend - 12 ||
+			    (int64_t)ip + len > (int64_t)iend - 8) {
+				if ((int64_t)ip + len != (int64_t)iend ||
+				    (int64_t)op + len > (int64_t)oend) {
+					lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
+					continue;
+				}
+				for (uint32_t i = gl; i < len; i += GS)
+					g.out[op + i] = (uint8_t)lz4e_in_rd8(g.in, ip + i);
+				lz4e_dgroup_finish(a, g, (int32_t)(op + len), gmask, gl);
+				continue;
+			}
+		}
+		/* literals */
+		for (uint32_t i = gl; i < len; i += GS)
+			g.out[op + i] = (uint8_t)lz4e_in_rd8(g.in, ip + i);
+		ip += len;
+		op += len;
+
+		/* offset, :280-283 */
+		const uint32_t offset =
+			lz4e_in_rd8(g.in, ip) | (lz4e_in_rd8(g.in, ip + 1) << 8);
+		uint32_t mlen = token & 15u;
+
+		ip += 2;
+		if (offset > op) { /* :299-302 */
+			lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
+			continue;
+		}
+		const bool full_shortcut = shortcut && mlen != 15u && offset >= 8u;
+
+		if (mlen == 15u) { /* :316-334 */
+			uint32_t s;
+			bool bad = false;
+
+			do {
+				s = lz4e_in_rd8(g.in, ip++);
+				if ((int32_t)ip > iend - 5) {
+					bad = true;
+					break;
+				}
+				mlen += s;
+			} while (s == 255u);
+			if (bad) {
+				lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
+				continue;
+			}
+		}
+		mlen += 4u;
+		if (!full_shortcut &&
+		    (int64_t)op + mlen > (int64_t)oend - 5) { /* :420-431 */
+			lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
+			continue;
+		}
+
+		/* match: literals (and everything earlier) must be visible */
+		lz4e_syncwarp(gmask);
+		if (offset == 0u) {
+			for (uint32_t i = gl; i < mlen; i += GS)
+				g.out[op + i] = 0;
+		} else if (offset >= mlen) {
+			const uint8_t *ms = g.out + (op - offset);
+
+			for (uint32_t i = gl; i < mlen; i += GS)
+				g.out[op + i] = ms[i];
+		} else {
+			const uint8_t *ms = g.out + (op - offset);
+
+			for (uint32_t i = gl; i < mlen; i += GS)
+				g.out[op + i] = ms[i % offset];
+		}
+		op += mlen;
+		g.ip = ip;
+		g.op = op;
+	}
+}
+
+template <int GS>
+LZ4E_DEV void lz4e_decompress_warp(const lz4e_decompress_args &a, uint8_t *sm,
+				   uint32_t slot0, uint32_t lane)
+{
+	if (a.stage_cap)
+		lz4e_decompress_warp_impl<GS, true>(a, sm, slot0, lane);
+	else
+		lz4e_decompress_warp_impl<GS, false>(a, sm, slot0, lane);
+}
+
+#endif /* LZ4E_DECOMPRESS_BODY_CUH */

@@ -1,0 +1,61 @@
+/*
+ * lz4e_simt.h — the few warp-level primitives the LZ4E kernels are written
+ * against.
+ *
+ * Under nvcc these map 1:1 to the CUDA intrinsics.  The kernel BODIES
+ * (lz4e_compress_body.cuh, lz4e_decompress_body.cuh) use only these names, so
+ * tests/simt/ can also compile the very same source with g++ against a
+ * coroutine-based 32-lane emulator and check the warp-cooperative logic
+ * (speculative search batches, in-order commit, sub-warp groups) against the
+ * oracle on machines without a GPU.  That emulator is TEST INFRASTRUCTURE: the
+ * product library contains only the nvcc build and has no CPU path.
+ */
+#ifndef LZ4E_SIMT_H
+#define LZ4E_SIMT_H
+
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+
+#define LZ4E_DEV __device__ __forceinline__
+#define LZ4E_FULL 0xffffffffu
+/* address-space hint for pointers rebuilt from 64-bit descriptor fields */
+#define LZ4E_ASSUME_GLOBAL(p) __builtin_assume(__isGlobal(p))
+
+LZ4E_DEV uint32_t lz4e_ballot(uint32_t mask, int pred)
+{
+	return __ballot_sync(mask, pred);
+}
+LZ4E_DEV uint32_t lz4e_shfl(uint32_t mask, uint32_t v, int src)
+{
+	return __shfl_sync(mask, v, src);
+}
+LZ4E_DEV uint32_t lz4e_match_any(uint32_t mask, uint32_t v)
+{
+	return __match_any_sync(mask, v);
+}
+LZ4E_DEV void lz4e_syncwarp(uint32_t mask)
+{
+	__syncwarp(mask);
+}
+LZ4E_DEV uint32_t lz4e_funnel_r(uint32_t lo, uint32_t hi, uint32_t sh)
+{
+	return __funnelshift_r(lo, hi, sh);
+}
+LZ4E_DEV int lz4e_clz(uint32_t v) { return __clz((int)v); }
+LZ4E_DEV int lz4e_ffs(uint32_t v) { return __ffs((int)v); }
+LZ4E_DEV int lz4e_popc(uint32_t v) { return __popc(v); }
+LZ4E_DEV uint32_t lz4e_atomic_add(uint32_t *p, uint32_t v)
+{
+	return atomicAdd(p, v);
+}
+LZ4E_DEV void lz4e_atomic_or(uint32_t *p, uint32_t v) { atomicOr(p, v); }
+LZ4E_DEV uint32_t lz4e_min(uint32_t a, uint32_t b) { return a < b ? a : b; }
+
+#else /* host build for tests/simt */
+
+#include "simt_host.h"
+
+#endif
+
+#endif /* LZ4E_SIMT_H */
