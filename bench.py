@@ -1,0 +1,528 @@
+#!/usr/bin/env python
+"""bench.py — LZ4E hot path benchmark (driver contract in the task statement).
+
+A "step" is one pass of the hot path over one batch of synthetic blocks:
+LZ4E_compress_default on every block, then the LZ4E decompressor on every
+compressed block (device-level C ABI, inputs resident in HBM).
+
+  N=1 workload  = BASELINE.json configs[1]: 1 GiB of independent 4 KiB blocks, one
+                  bvec each (byU16), content class = block index mod 4.
+  N>1           = weak scaling: every rank owns 1 GiB of the N GiB batch, sharded by
+                  block index, no collective on the data path.
+  extra.cfg3_64k = a 2 GiB subset of configs[2] (64 KiB blocks over 16 odd,
+                  non-contiguous segments, mid-bvec iterator start) on rank 0.
+
+  --impl reference  times the reference's own C code (oracle/_ref, built from
+                  /root/reference's sources unmodified; else the oracle port) on the
+                  host cores, on a bounded sample of the same workload.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "compress & decompress input GB/s at 4/64 KiB blocks, 1/2/4/8 B200, byte-identical"
+BLOCK = 4096
+BLOCKS_PER_GPU = 262144          # 1 GiB
+DST_STRIDE = 4224                # >= LZ4E_COMPRESSBOUND(4096) = 4128, multiple of 128
+CFG3_BLOCKS = 32768              # 2 GiB subset of config 3
+CFG3_SIZE = 65536
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu, self.lines, self.proc = gpu, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- workloads
+def cfg2_tables(pkg, src_base, dst_base, out_base, nblocks):
+    """4 KiB blocks, one bvec each; destination = one (multi-page) bvec of COMPRESSBOUND."""
+    idx = np.arange(nblocks, dtype=np.uint64)
+    bound = pkg.compress_bound(BLOCK)
+
+    def tab(base, stride, length):
+        bv = np.zeros(nblocks, dtype=pkg.DEV_BVEC)
+        bv["addr"] = np.uint64(base) + idx * np.uint64(stride)
+        bv["len"] = length
+        it = np.zeros(nblocks, dtype=pkg.DEV_ITER)
+        it["first"] = idx.astype(np.uint32)
+        it["bi_size"] = length
+        return bv, it
+    return tab(src_base, BLOCK, BLOCK), tab(dst_base, DST_STRIDE, bound), tab(out_base, BLOCK, BLOCK)
+
+
+def cfg3_tables(pkg, base, nblocks, size, capacity, salt):
+    """`size`-byte blocks over 16 non-contiguous segments with odd offsets and lengths and a
+    mid-bvec iterator start; each segment owns a private run of 3 pages."""
+    nseg = 16
+    b = np.arange(nblocks, dtype=np.int64)[:, None]
+    i = np.arange(nseg, dtype=np.int64)[None, :]
+    per = capacity // nseg
+    delta = ((b * 31 + i * 17 + salt) % 129) - 64
+    delta = np.where(i % 2 == 1, -delta, delta)
+    lens = per + delta
+    skip = 1 + ((b[:, 0] * 2654435761 + salt) >> 7) % 4095
+    lens[:, 0] += skip
+    lens[:, -1] += capacity - (lens.sum(axis=1) - skip)
+    offs = (53 * (i + b) + 7 + salt) % 509
+    assert (lens > 0).all() and (offs + lens <= 3 * 4096).all()
+    seg_index = (b * nseg + i).astype(np.uint64)
+    bv = np.zeros(nblocks * nseg, dtype=pkg.DEV_BVEC)
+    bv["addr"] = (np.uint64(base) + seg_index * np.uint64(3 * 4096) + offs.astype(np.uint64)).reshape(-1)
+    bv["len"] = lens.reshape(-1).astype(np.uint32)
+    it = np.zeros(nblocks, dtype=pkg.DEV_ITER)
+    it["first"] = (np.arange(nblocks) * nseg).astype(np.uint32)
+    it["bi_size"] = size
+    it["bi_bvec_done"] = skip.astype(np.uint32)
+    return bv, it, nblocks * nseg * 3 * 4096
+
+
+def event_ms(torch, fn, stream):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    fn()
+    e1.record(stream)
+    return e0, e1
+
+
+# ----------------------------------------------------------------------------- product arm
+def run_ours(args):
+    import torch
+    pkg = importlib.import_module("lz4-sgori_b200")
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    ctx = pkg.Context(local)          # raises without a B200: no CPU path
+    stream = torch.cuda.Stream(device=local)
+    sp = stream.cuda_stream
+
+    total_blocks = BLOCKS_PER_GPU * world
+    first, count = pkg.shard_range(total_blocks, rank, world)
+    nb = int(count)
+    in_bytes = nb * BLOCK
+
+    # ---- device-resident batch (config 2 shard) ----
+    d_src = ctx.dev_alloc(nb * BLOCK)
+    d_dst = ctx.dev_alloc(nb * DST_STRIDE)
+    d_out = ctx.dev_alloc(nb * BLOCK)
+    (sbv, sit), (dbv, dit), (obv, oit) = cfg2_tables(pkg, d_src, d_dst, d_out, nb)
+    t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
+    d_rets, d_rets2 = ctx.dev_alloc(4 * nb), ctx.dev_alloc(4 * nb)
+    ctx.synth_fill_dev(t[0], t[1], nb, first_index=int(first), stream=sp)
+    ctx.sync(sp)
+    ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, stream=sp)
+    ctx.sync(sp)
+    rets = ctx.download(d_rets, np.int32, nb)
+    assert (rets > 0).all()
+    comp_bytes = int(rets.sum())
+    cit = dit.copy()
+    cit["bi_size"] = rets.astype(np.uint32)
+    d_cit = ctx.upload(cit)
+    max_c = int(rets.max())
+
+    def step(evs=None):
+        if evs is not None:
+            evs.append(event_ms(torch, lambda: ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK,
+                                                                d_rets, stream=sp), stream))
+            evs.append(event_ms(torch, lambda: ctx.decompress_dev(
+                t[2], d_cit, t[4], t[5], nb, max_c, BLOCK, d_rets2, flags=pkg.DEV_DST_LINEAR,
+                stream=sp), stream))
+        else:
+            ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, stream=sp)
+            ctx.decompress_dev(t[2], d_cit, t[4], t[5], nb, max_c, BLOCK, d_rets2,
+                               flags=pkg.DEV_DST_LINEAR, stream=sp)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    ctx.sync(sp)
+    # round-trip check on the warm-up result (size-independent property at full size)
+    r2 = ctx.download(d_rets2, np.int32, nb)
+    assert (r2 == BLOCK).all(), "round trip sizes"
+    a = torch.empty(0)  # noqa: F841
+    src_t = ctx.download(d_src, np.uint8, min(in_bytes, 64 << 20))
+    out_t = ctx.download(d_out, np.uint8, min(in_bytes, 64 << 20))
+    assert np.array_equal(src_t, out_t), "round trip bytes"
+    del src_t, out_t
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    l0 = ctx.launches()
+    evs = []
+    barrier()
+    sampler.start()
+    e_begin, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e_begin.record(stream)
+    for _ in range(args.steps):
+        step(evs)
+    e_end.record(stream)
+    ctx.sync(sp)
+    barrier()
+    clocks = sampler.stop()
+    launches = ctx.launches() - l0
+    total_ms = e_begin.elapsed_time(e_end)
+    c_ms = float(np.mean([a.elapsed_time(b) for a, b in evs[0::2]]))
+    d_ms = float(np.mean([a.elapsed_time(b) for a, b in evs[1::2]]))
+    if dist is not None:
+        tt = torch.tensor([total_ms, c_ms, d_ms], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total_ms, c_ms, d_ms = [float(x) for x in tt.tolist()]
+        cb = torch.tensor([comp_bytes], device=f"cuda:{local}", dtype=torch.int64)
+        dist.all_reduce(cb)
+        comp_total = int(cb.item())
+    else:
+        comp_total = comp_bytes
+    ms_per_step = total_ms / args.steps
+    job_in = total_blocks * BLOCK
+
+    result = None
+    if rank == 0:
+        peak, peak_src = peaks()
+        c_gbs = job_in / (c_ms * 1e-3) / 1e9
+        d_gbs = job_in / (d_ms * 1e-3) / 1e9
+        alg = (job_in + comp_total) / world    # N + C per launch (per GPU)
+        dom = "lz4e_compress_kernel" if c_ms >= d_ms else "lz4e_decompress_kernel"
+        dom_ms = max(c_ms, d_ms)
+        ach = alg / (dom_ms * 1e-3) / 1e9
+        result = {
+            "metric": METRIC,
+            "value": round(job_in / (ms_per_step * 1e-3) / 1e9, 3),
+            "unit": "GB/s of uncompressed input through compress+decompress (one step = both passes)",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "configs[1]: %d x 4 KiB blocks per GPU (1 GiB/GPU), 1 bvec each "
+                                   "(byU16), class = block index mod 4 (text/random/sparse/mixed), "
+                                   "dst capacity LZ4E_COMPRESSBOUND" % BLOCKS_PER_GPU,
+                       "l2": "inputs (1 GiB per GPU) exceed the 126 MB L2; no explicit flush",
+                       "sharding": "contiguous block ranges per rank, no collective"},
+            "compress_gbs": round(c_gbs, 3), "decompress_gbs": round(d_gbs, 3),
+            "decompress_compressed_in_gbs": round(comp_total / (d_ms * 1e-3) / 1e9, 3),
+            "ratio": round(job_in / comp_total, 4),
+            "kernel_ms": {"compress": round(c_ms, 4), "decompress": round(d_ms, 4)},
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(ach, 2), "peak": peak,
+                         "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak, 5),
+                         "traffic": None,
+                         "algorithmic_bytes_per_launch": int(alg)},
+            "roofline_other": {
+                "kernel": "lz4e_decompress_kernel" if dom.startswith("lz4e_c") else "lz4e_compress_kernel",
+                "achieved": round(alg / (min(c_ms, d_ms) * 1e-3) / 1e9, 2),
+                "frac": round(alg / (min(c_ms, d_ms) * 1e-3) / 1e9 / peak, 5)},
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+    for p in (d_src, d_dst, d_out, d_rets, d_rets2, d_cit, *t):
+        ctx.dev_free(p)
+
+    if rank == 0 and not args.no_extra:
+        try:
+            result["extra"] = {"cfg3_64k": run_cfg3(torch, pkg, ctx, stream, args)}
+        except Exception as e:  # the headline line must still print
+            result["extra"] = {"cfg3_64k": {"error": repr(e)}}
+    if rank == 0 and world == 1 and not args.no_e2e:
+        result["e2e"] = run_e2e(torch, pkg, ctx, args)
+    elif rank == 0:
+        result["e2e"] = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        result["cpu_baseline"] = cpu_baseline(pkg, budget_s=args.cpu_seconds)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(result))
+    ctx.close()
+
+
+def run_cfg3(torch, pkg, ctx, stream, args):
+    """2 GiB subset of config 3 on one GPU: 64 KiB blocks, 16 odd segments both sides."""
+    sp = stream.cuda_stream
+    nb = CFG3_BLOCKS
+    bound = pkg.compress_bound(CFG3_SIZE)
+    region = nb * 16 * 3 * 4096
+    d_src, d_dst, d_out = ctx.dev_alloc(region), ctx.dev_alloc(region), ctx.dev_alloc(region)
+    sbv, sit, _ = cfg3_tables(pkg, d_src, nb, CFG3_SIZE, CFG3_SIZE, 0)
+    dbv, dit, _ = cfg3_tables(pkg, d_dst, nb, bound, bound, 11)
+    obv, oit, _ = cfg3_tables(pkg, d_out, nb, CFG3_SIZE, CFG3_SIZE, 5)
+    t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
+    d_rets, d_rets2 = ctx.dev_alloc(4 * nb), ctx.dev_alloc(4 * nb)
+    ctx.synth_fill_dev(t[0], t[1], nb, first_index=0, stream=sp)
+    ctx.compress_dev(t[0], t[1], t[2], t[3], nb, CFG3_SIZE, d_rets, flags=pkg.DEV_NO_BYU16, stream=sp)
+    ctx.sync(sp)
+    rets = ctx.download(d_rets, np.int32, nb)
+    assert (rets > 0).all()
+    cit = dit.copy()
+    cit["bi_size"] = rets.astype(np.uint32)
+    d_cit = ctx.upload(cit)
+    cms, dms = [], []
+    for it in range(2 + 3):
+        ec = event_ms(torch, lambda: ctx.compress_dev(t[0], t[1], t[2], t[3], nb, CFG3_SIZE, d_rets,
+                                                      flags=pkg.DEV_NO_BYU16, stream=sp), stream)
+        ed = event_ms(torch, lambda: ctx.decompress_dev(t[2], d_cit, t[4], t[5], nb, int(rets.max()),
+                                                        CFG3_SIZE, d_rets2, stream=sp), stream)
+        ctx.sync(sp)
+        if it >= 2:
+            cms.append(ec[0].elapsed_time(ec[1]))
+            dms.append(ed[0].elapsed_time(ed[1]))
+    r2 = ctx.download(d_rets2, np.int32, nb)
+    assert (r2 == CFG3_SIZE).all(), "64k round trip sizes"
+    nbytes, cbytes = nb * CFG3_SIZE, int(rets.sum())
+    peak, _ = peaks()
+    c_ms, d_ms = float(np.mean(cms)), float(np.mean(dms))
+    for p in (d_src, d_dst, d_out, d_rets, d_rets2, d_cit, *t):
+        ctx.dev_free(p)
+    return {"workload": "configs[2] subset: %d x 64 KiB blocks (2 GiB), 16 odd non-contiguous "
+                        "segments per side, mid-bvec start (byU32)" % nb,
+            "compress_gbs": round(nbytes / (c_ms * 1e-3) / 1e9, 3),
+            "decompress_gbs": round(nbytes / (d_ms * 1e-3) / 1e9, 3),
+            "ratio": round(nbytes / cbytes, 4),
+            "kernel_ms": {"compress": round(c_ms, 3), "decompress": round(d_ms, 3)},
+            "decompress_roofline_frac": round((nbytes + cbytes) / (d_ms * 1e-3) / 1e9 / peak, 5),
+            "compress_roofline_frac": round((nbytes + cbytes) / (c_ms * 1e-3) / 1e9 / peak, 5)}
+
+
+def run_e2e(torch, pkg, ctx, args):
+    """The same step through the reference-facing host API (lz4e_b200_compress_batch /
+    lz4e_b200_decompress_batch = LZ4E_compress_default per block) with HOST buffers in pinned
+    page arenas: host<->device copies of pages, descriptor tables and results are inside the
+    timed region."""
+    sg = pkg.sg
+    nb = args.e2e_blocks
+    src_arena = pkg.Arena(ctx, nb + 1)
+    dst_pages = (nb * DST_STRIDE + 4095) // 4096 + 2
+    dst_arena = pkg.Arena(ctx, dst_pages)
+    out_arena = pkg.Arena(ctx, nb + 1)
+    bound = pkg.compress_bound(BLOCK)
+    idx = np.arange(nb, dtype=np.uint64)
+
+    def lay(arena, stride, length):
+        bv = np.zeros(nb, dtype=pkg.BIO_VEC)
+        a = np.uint64(arena.base) + idx * np.uint64(stride)
+        bv["bv_page"] = a & ~np.uint64(4095)
+        bv["bv_offset"] = (a & np.uint64(4095)).astype(np.uint32)
+        bv["bv_len"] = length
+        it = np.zeros(nb, dtype=pkg.BVEC_ITER)
+        it["bi_size"] = length
+        return sg.Layout(arena, bv, idx.copy(), it, arena.npages)
+    src, dst, out = lay(src_arena, BLOCK, BLOCK), lay(dst_arena, DST_STRIDE, bound), \
+        lay(out_arena, BLOCK, BLOCK)
+    mem = src_arena.mem[:nb * BLOCK].reshape(nb, BLOCK)
+    for b in range(nb):
+        pkg.lib().lz4e_b200_synth_fill_host(mem[b].ctypes.data, BLOCK, b & 3, b)
+    creqs, keep1 = pkg.make_reqs(src, dst)
+
+    def once():
+        creqs["ret"] = 0
+        rc = ctx.compress_batch(creqs, flags=pkg.F_KEEP_ITERS)
+        assert rc == 0, ctx.err()
+        sizes = creqs["ret"].copy()
+        csrc = sg.Layout(dst_arena, dst.bvecs, dst.first, dst.iters.copy(), dst.npages_used)
+        csrc.iters["bi_size"] = sizes.astype(np.uint32)
+        dreqs, keep2 = pkg.make_reqs(csrc, out)
+        rc = ctx.decompress_batch(dreqs, flags=0)
+        assert rc == 0, ctx.err()
+        return sizes, dreqs["ret"].copy()
+
+    for _ in range(2):
+        sizes, r2 = once()
+    assert (sizes > 0).all() and (r2 == BLOCK).all()
+    assert np.array_equal(out_arena.mem[:nb * BLOCK], src_arena.mem[:nb * BLOCK]), "e2e round trip"
+    reps = 3
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        once()
+    dt = (time.perf_counter() - t0) / reps
+    tables = nb * (16 + 16 + 16 + 16)
+    h2d = nb * BLOCK + tables + int(sizes.sum() // 1) + tables     # pages + tables, both passes (approx. ranges)
+    h2d = nb * BLOCK + tables + nb * DST_STRIDE + tables
+    d2h = nb * DST_STRIDE + nb * 12 + nb * BLOCK + nb * 12
+    for a in (src_arena, dst_arena, out_arena):
+        a.close()
+    return {"value": round(nb * BLOCK / dt / 1e9, 3),
+            "unit": "GB/s of uncompressed input through compress+decompress, host buffers",
+            "blocks": nb, "ms_per_step": round(dt * 1e3, 3),
+            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+            "api": "lz4e_b200_compress_batch + lz4e_b200_decompress_batch (pinned page arenas)"}
+
+
+# ----------------------------------------------------------------------------- CPU arms
+def cpu_sample(pkg, nblocks, first_index=0):
+    """Host copy of the first `nblocks` blocks of the config-2 workload + bio_vec tables."""
+    sg = pkg.sg
+    arena = sg.HostArena(nblocks + 1)
+    specs = [sg.segs_single(BLOCK)] * nblocks
+    src = sg.layout_from_segments(arena, [dict(s, gap=0) for s in specs])
+    mem = arena.mem[:nblocks * BLOCK].reshape(nblocks, BLOCK)
+    for b in range(nblocks):
+        pkg.lib().lz4e_b200_synth_fill_host(mem[b].ctypes.data, BLOCK, (first_index + b) & 3,
+                                            first_index + b)
+    bound = pkg.compress_bound(BLOCK)
+    darena = sg.HostArena(nblocks * 2 + 1)
+    dst = sg.layout_from_segments(darena, [dict(sg.segs_single(bound), gap=0)] * nblocks)
+    return src, dst
+
+
+def cpu_run(pkg, lib, src, dst, threads):
+    """One CPU step on a sample: compress every block, then decompress every block."""
+    from oracle import oracle
+    n = src.nblocks()
+    rets, t_c = oracle.compress_batch(lib, src.bvecs, src.first, src.iters, dst.bvecs, dst.first,
+                                      dst.iters, nthreads=threads)
+    assert (rets > 0).all()
+    doff = (dst.bvecs["bv_page"] - np.uint64(dst.arena.base)).astype(np.uint64)
+    outbuf = np.zeros(n * BLOCK + 64, dtype=np.uint8)
+    r2, t_d = oracle.decompress_batch(lib, dst.arena.mem, doff, rets, outbuf,
+                                      np.arange(n, dtype=np.uint64) * np.uint64(BLOCK),
+                                      np.full(n, BLOCK, dtype=np.int32), nthreads=threads)
+    assert (r2 == BLOCK).all()
+    return t_c, t_d
+
+
+def cpu_baseline(pkg, budget_s=12.0):
+    from oracle import oracle
+    lib = oracle.load("auto")
+    threads = os.cpu_count() or 1
+    src, dst = cpu_sample(pkg, 1024)
+    t_c, t_d = cpu_run(pkg, lib, src, dst, threads)
+    per_block = (t_c + t_d) / 1024
+    n = int(min(max(budget_s / max(per_block, 1e-9), 2048), 65536))
+    src, dst = cpu_sample(pkg, n)
+    t_c, t_d = cpu_run(pkg, lib, src, dst, threads)
+    nbytes = n * BLOCK
+    return {"value": round(nbytes / (t_c + t_d) / 1e9, 4),
+            "unit": "GB/s of uncompressed input through compress+decompress",
+            "cores": threads, "kind": "reference" if lib.kind == "reference" else "port",
+            "sample": "first %d blocks (%d MiB) of the configs[1] workload, one block per task, "
+                      "one thread per core with its own wrkmem" % (n, nbytes >> 20),
+            "compress_gbs": round(nbytes / t_c / 1e9, 4), "decompress_gbs": round(nbytes / t_d / 1e9, 4)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own C implementation of the path on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pkg = importlib.import_module("lz4-sgori_b200")
+    from oracle import oracle
+    lib = oracle.load("auto")
+    threads = os.cpu_count() or 1
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    src, dst = cpu_sample(pkg, 512)
+    t_c, t_d = cpu_run(pkg, lib, src, dst, threads)
+    per_block = (t_c + t_d) / 512
+    total_steps = args.steps + args.warmup
+    n = int(min(max(60.0 / total_steps / max(per_block, 1e-9), 1024), 32768))
+    src, dst = cpu_sample(pkg, n)
+    for _ in range(args.warmup):
+        cpu_run(pkg, lib, src, dst, threads)
+    tc = td = 0.0
+    for _ in range(args.steps):
+        a, b = cpu_run(pkg, lib, src, dst, threads)
+        tc, td = tc + a, td + b
+    nbytes = n * BLOCK * args.steps
+    val = round(nbytes / (tc + td) / 1e9, 4)
+    unit = "GB/s of uncompressed input through compress+decompress (one step = both passes)"
+    kind = "reference" if lib.kind == "reference" else "port"
+    sample = ("each step = first %d blocks (%d MiB) of the configs[1] workload; whole job is %d GiB"
+              % (n, (n * BLOCK) >> 20, world))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": unit, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round((tc + td) / args.steps * 1e3, 3), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "configs[1]: 4 KiB blocks, 1 bvec each (byU16), class = block index "
+                               "mod 4; CPU arm runs a bounded sample per step",
+                   "sample": sample},
+        "compress_gbs": round(nbytes / tc / 1e9, 4), "decompress_gbs": round(nbytes / td / 1e9, 4),
+        "cpu_baseline": {"value": val, "unit": unit, "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-blocks", type=int, default=BLOCKS_PER_GPU)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

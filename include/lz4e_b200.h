@@ -93,6 +93,14 @@ int lz4e_b200_sync(lz4e_b200_ctx *ctx, void *stream);
 
 /* ---- layer 1: device-level batches --------------------------------------- */
 
+/* promises a caller of a *_dev entry point may make (checked on the device,
+ * a broken promise raises LZ4E_B200_ERANGE at the next lz4e_b200_sync) */
+#define LZ4E_B200_DEV_NO_BYU16 1u   /* compress: no block selects the byU16 table
+				     * (every block has a bv_len > 4096 or more
+				     * than 16 bvecs): halves the table footprint */
+#define LZ4E_B200_DEV_DST_LINEAR 2u /* decompress: every destination is one
+				     * contiguous segment: no scratch needed */
+
 /*
  * LZ4E_compress_default for `nblocks` independent blocks.
  *  src_bvecs/src_iters   source tables (device memory)
@@ -112,7 +120,8 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 			   const struct lz4e_b200_dev_bvec *dst_bvecs,
 			   const struct lz4e_b200_dev_iter *dst_iters,
 			   uint32_t nblocks, uint32_t max_in_bytes,
-			   int32_t *rets, struct lz4e_b200_dev_end *ends);
+			   uint32_t flags, int32_t *rets,
+			   struct lz4e_b200_dev_end *ends);
 
 /*
  * LZ4E decompression (lz4e/lz4e_decompress.c:462-470 semantics on the
@@ -126,22 +135,27 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 			     const struct lz4e_b200_dev_bvec *dst_bvecs,
 			     const struct lz4e_b200_dev_iter *dst_iters,
 			     uint32_t nblocks, uint32_t max_in_bytes,
-			     uint32_t max_out_bytes, int32_t *rets);
+			     uint32_t max_out_bytes, uint32_t flags,
+			     int32_t *rets);
 
 /*
  * Compacted-output compression (SURVEY.md section 8b, item iii): all blocks
- * are written back to back into ONE destination stream described by
- * dst_bvecs/dst_stream.  Blocks are compressed into context scratch, a device
- * prefix scan over rets[] yields offsets[b] (exclusive, nblocks+1 entries)
- * and a scatter kernel packs them.  A block that fails (ret 0) takes no space.
- * Capacity per block is LZ4E_COMPRESSBOUND (noLimit mode).
+ * are written back to back into ONE destination SG stream: dst_bvecs[0 ..
+ * dst_nbvecs), starting dst_bvec_done bytes into dst_bvecs[0], at most
+ * dst_capacity bytes.  Blocks are compressed into context scratch (capacity
+ * LZ4E_COMPRESSBOUND each, i.e. the reference's noLimit mode), a device prefix
+ * scan over rets[] yields offsets[b] (exclusive; nblocks + 1 entries, the last
+ * one is the total) and a pack kernel moves every block to its offset.  A
+ * block that fails (ret 0) takes no space; running out of dst_capacity raises
+ * LZ4E_B200_ERANGE at the next lz4e_b200_sync().
  */
 int lz4e_b200_compress_compact_dev(lz4e_b200_ctx *ctx, void *stream,
 				   const struct lz4e_b200_dev_bvec *src_bvecs,
 				   const struct lz4e_b200_dev_iter *src_iters,
 				   const struct lz4e_b200_dev_bvec *dst_bvecs,
-				   const struct lz4e_b200_dev_iter *dst_stream,
-				   uint32_t nblocks, uint32_t max_in_bytes,
+				   uint32_t dst_nbvecs, uint32_t dst_bvec_done,
+				   uint64_t dst_capacity, uint32_t nblocks,
+				   uint32_t max_in_bytes, uint32_t flags,
 				   int32_t *rets, uint64_t *offsets);
 
 /* Fill SG blocks with the synthetic benchmark contents of
@@ -155,6 +169,17 @@ int lz4e_b200_synth_fill_dev(lz4e_b200_ctx *ctx, void *stream,
 void lz4e_b200_synth_fill_host(uint8_t *buf, uint32_t n, uint32_t cls,
 			       uint32_t seed);
 
+/* ---- raw memory helpers for the C host library --------------------------- */
+void *lz4e_b200_dev_alloc(lz4e_b200_ctx *ctx, size_t bytes);
+void lz4e_b200_dev_free(lz4e_b200_ctx *ctx, void *p);
+void *lz4e_b200_host_alloc(lz4e_b200_ctx *ctx, size_t bytes); /* pinned */
+void lz4e_b200_host_free(lz4e_b200_ctx *ctx, void *p);
+/* asynchronous on `stream` (NULL = the context's stream) */
+int lz4e_b200_copy_h2d(lz4e_b200_ctx *ctx, void *stream, void *dst_dev,
+		       const void *src_host, size_t bytes);
+int lz4e_b200_copy_d2h(lz4e_b200_ctx *ctx, void *stream, void *dst_host,
+		       const void *src_dev, size_t bytes);
+
 /* ---- layer 2: page arenas ------------------------------------------------ */
 int lz4e_b200_arena_create(lz4e_b200_ctx *ctx, size_t npages,
 			   lz4e_b200_arena **out);
@@ -166,6 +191,10 @@ int lz4e_b200_arena_upload(lz4e_b200_arena *arena, size_t first_page,
 			   size_t npages);
 int lz4e_b200_arena_download(lz4e_b200_arena *arena, size_t first_page,
 			     size_t npages);
+/* device address mirroring host address `p` if it lies in an arena of ctx,
+ * else 0; *arena_out (optional) receives the arena */
+uint64_t lz4e_b200_arena_translate(lz4e_b200_ctx *ctx, const void *p,
+				   lz4e_b200_arena **arena_out);
 
 /* ---- layer 3: host-level batches ----------------------------------------- */
 
@@ -182,6 +211,12 @@ struct lz4e_b200_req {
 #define LZ4E_B200_F_SRC_RESIDENT 1u /* source pages already current on device */
 #define LZ4E_B200_F_DST_ON_DEVICE 2u /* leave results in the device mirror */
 #define LZ4E_B200_F_KEEP_ITERS 4u   /* do not move the iterators */
+/* Destination pages that live in an arena come back with ONE bulk copy of the
+ * touched byte range [first, last] of that arena, so host bytes inside that
+ * range which the kernels did not write are replaced by the device mirror's.
+ * With DST_PRESERVE the range is uploaded first, which keeps every unwritten
+ * byte exactly as it was (what a lone LZ4E_compress_default call does). */
+#define LZ4E_B200_F_DST_PRESERVE 8u
 
 /* Pages may live in an arena (fast path: one bulk copy per arena per
  * direction) or anywhere in host memory (bounced segment by segment). */

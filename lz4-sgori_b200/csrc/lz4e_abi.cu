@@ -1,0 +1,541 @@
+/*
+ * lz4e_abi.cu — implementation of the C ABI declared in include/lz4e_b200.h:
+ * context, page arenas, raw memory helpers and the device-level batch entry
+ * points.  Everything here either enqueues CUDA work or fails with an error
+ * code; there is no CPU implementation of the codec in this library.
+ */
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "../../include/lz4e_b200.h"
+#include "lz4e_compress_body.cuh"
+#include "lz4e_decompress_body.cuh"
+#include "lz4e_kernels.h"
+#include "lz4e_synth.h"
+
+#define CTL_COUNTERS 256
+#define CTL_FAULTS CTL_COUNTERS
+#define CTL_WORDS (CTL_COUNTERS + 8)
+
+struct lz4e_b200_arena {
+	lz4e_b200_ctx *ctx;
+	uint8_t *host;
+	uint8_t *dev;
+	size_t npages;
+};
+
+struct lz4e_b200_ctx {
+	int device;
+	int sm_count;
+	cudaStream_t stream;
+	uint32_t *d_ctl; /* work counters + fault word */
+	std::atomic<uint32_t> ctl_next;
+	std::atomic<uint64_t> launches;
+	uint8_t *scratch;
+	size_t scratch_bytes;
+	std::mutex mu;
+	std::vector<lz4e_b200_arena *> arenas;
+	char err[256];
+	int dgroup;  /* decompression group size: 8, 16 or 32 */
+	int dstage;  /* -1 auto, 0 never stage, 1 stage when it fits */
+};
+
+static void set_err(lz4e_b200_ctx *ctx, const char *fmt, ...)
+{
+	va_list ap;
+
+	if (!ctx)
+		return;
+	va_start(ap, fmt);
+	vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
+	va_end(ap);
+}
+
+#define CU(ctx, call)                                                        \
+	do {                                                                 \
+		cudaError_t e_ = (call);                                     \
+		if (e_ != cudaSuccess) {                                     \
+			set_err(ctx, "%s failed: %s", #call,                 \
+				cudaGetErrorString(e_));                     \
+			return LZ4E_B200_EIO;                                \
+		}                                                            \
+	} while (0)
+
+static cudaStream_t pick(lz4e_b200_ctx *ctx, void *stream)
+{
+	return stream ? (cudaStream_t)stream : ctx->stream;
+}
+
+extern "C" {
+
+int lz4e_b200_device_count(void)
+{
+	int n = 0;
+
+	if (cudaGetDeviceCount(&n) != cudaSuccess)
+		return 0;
+	return n;
+}
+
+int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
+{
+	cudaDeviceProp prop;
+	int n = 0;
+
+	if (!out)
+		return LZ4E_B200_EINVAL;
+	*out = nullptr;
+	if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) {
+		fprintf(stderr,
+			"lz4e_b200: no usable CUDA device %d (found %d); this library "
+			"has no CPU path\n",
+			device, n);
+		return LZ4E_B200_ENODEV;
+	}
+	if (cudaSetDevice(device) != cudaSuccess ||
+	    cudaGetDeviceProperties(&prop, device) != cudaSuccess)
+		return LZ4E_B200_ENODEV;
+	if (prop.major < 10) {
+		fprintf(stderr,
+			"lz4e_b200: device %d is sm_%d%d; kernels are built for sm_100a only\n",
+			device, prop.major, prop.minor);
+		return LZ4E_B200_ENODEV;
+	}
+	lz4e_b200_ctx *ctx = new lz4e_b200_ctx();
+
+	ctx->device = device;
+	ctx->sm_count = prop.multiProcessorCount;
+	ctx->ctl_next = 0;
+	ctx->launches = 0;
+	ctx->scratch = nullptr;
+	ctx->scratch_bytes = 0;
+	ctx->err[0] = 0;
+	ctx->dgroup = 8;
+	ctx->dstage = -1;
+	if (const char *e = getenv("LZ4E_B200_DGROUP")) {
+		int g = atoi(e);
+
+		if (g == 8 || g == 16 || g == 32)
+			ctx->dgroup = g;
+	}
+	if (const char *e = getenv("LZ4E_B200_DSTAGE"))
+		ctx->dstage = atoi(e) ? 1 : 0;
+	if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+	    cudaMalloc((void **)&ctx->d_ctl, CTL_WORDS * sizeof(uint32_t)) != cudaSuccess ||
+	    cudaMemset(ctx->d_ctl, 0, CTL_WORDS * sizeof(uint32_t)) != cudaSuccess) {
+		fprintf(stderr, "lz4e_b200: context setup failed: %s\n",
+			cudaGetErrorString(cudaGetLastError()));
+		delete ctx;
+		return LZ4E_B200_EIO;
+	}
+	*out = ctx;
+	return LZ4E_B200_OK;
+}
+
+void lz4e_b200_ctx_destroy(lz4e_b200_ctx *ctx)
+{
+	if (!ctx)
+		return;
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	cudaFree(ctx->scratch);
+	cudaFree(ctx->d_ctl);
+	cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+lz4e_b200_ctx *lz4e_b200_default_ctx(void)
+{
+	static std::mutex mu;
+	static lz4e_b200_ctx *def;
+	std::lock_guard<std::mutex> lk(mu);
+
+	if (!def) {
+		const char *e = getenv("LZ4E_B200_DEVICE");
+
+		if (lz4e_b200_ctx_create(e ? atoi(e) : 0, &def) != LZ4E_B200_OK)
+			def = nullptr;
+	}
+	return def;
+}
+
+const char *lz4e_b200_strerror(lz4e_b200_ctx *ctx)
+{
+	return ctx ? ctx->err : "no context";
+}
+
+int lz4e_b200_ctx_device(lz4e_b200_ctx *ctx) { return ctx->device; }
+int lz4e_b200_ctx_sm_count(lz4e_b200_ctx *ctx) { return ctx->sm_count; }
+uint64_t lz4e_b200_kernel_launches(lz4e_b200_ctx *ctx) { return ctx->launches.load(); }
+
+int lz4e_b200_sync(lz4e_b200_ctx *ctx, void *stream)
+{
+	uint32_t faults = 0;
+
+	cudaSetDevice(ctx->device);
+	CU(ctx, cudaStreamSynchronize(pick(ctx, stream)));
+	CU(ctx, cudaMemcpy(&faults, ctx->d_ctl + CTL_FAULTS, 4, cudaMemcpyDeviceToHost));
+	if (faults) {
+		CU(ctx, cudaMemset(ctx->d_ctl + CTL_FAULTS, 0, 4));
+		set_err(ctx, "device fault flags 0x%x: a block exceeded the limits or "
+			     "promises given to a *_dev call",
+			faults);
+		return LZ4E_B200_ERANGE;
+	}
+	return LZ4E_B200_OK;
+}
+
+/* ---- raw memory ---------------------------------------------------------- */
+void *lz4e_b200_dev_alloc(lz4e_b200_ctx *ctx, size_t bytes)
+{
+	void *p = nullptr;
+
+	cudaSetDevice(ctx->device);
+	if (cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) {
+		set_err(ctx, "cudaMalloc(%zu) failed", bytes);
+		return nullptr;
+	}
+	return p;
+}
+
+void lz4e_b200_dev_free(lz4e_b200_ctx *ctx, void *p)
+{
+	cudaSetDevice(ctx->device);
+	cudaFree(p);
+}
+
+void *lz4e_b200_host_alloc(lz4e_b200_ctx *ctx, size_t bytes)
+{
+	void *p = nullptr;
+
+	cudaSetDevice(ctx->device);
+	if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+		set_err(ctx, "cudaHostAlloc(%zu) failed", bytes);
+		return nullptr;
+	}
+	return p;
+}
+
+void lz4e_b200_host_free(lz4e_b200_ctx *ctx, void *p)
+{
+	cudaSetDevice(ctx->device);
+	cudaFreeHost(p);
+}
+
+int lz4e_b200_copy_h2d(lz4e_b200_ctx *ctx, void *stream, void *dst_dev,
+		       const void *src_host, size_t bytes)
+{
+	cudaSetDevice(ctx->device);
+	CU(ctx, cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice,
+				pick(ctx, stream)));
+	return LZ4E_B200_OK;
+}
+
+int lz4e_b200_copy_d2h(lz4e_b200_ctx *ctx, void *stream, void *dst_host,
+		       const void *src_dev, size_t bytes)
+{
+	cudaSetDevice(ctx->device);
+	CU(ctx, cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost,
+				pick(ctx, stream)));
+	return LZ4E_B200_OK;
+}
+
+/* ---- arenas -------------------------------------------------------------- */
+int lz4e_b200_arena_create(lz4e_b200_ctx *ctx, size_t npages, lz4e_b200_arena **out)
+{
+	lz4e_b200_arena *a;
+
+	if (!ctx || !out || !npages)
+		return LZ4E_B200_EINVAL;
+	cudaSetDevice(ctx->device);
+	a = new lz4e_b200_arena();
+	a->ctx = ctx;
+	a->npages = npages;
+	a->host = a->dev = nullptr;
+	if (cudaHostAlloc((void **)&a->host, npages * PAGE_SIZE, cudaHostAllocDefault) !=
+		    cudaSuccess ||
+	    cudaMalloc((void **)&a->dev, npages * PAGE_SIZE) != cudaSuccess) {
+		set_err(ctx, "arena of %zu pages: %s", npages,
+			cudaGetErrorString(cudaGetLastError()));
+		cudaFreeHost(a->host);
+		cudaFree(a->dev);
+		delete a;
+		return LZ4E_B200_ENOMEM;
+	}
+	{
+		std::lock_guard<std::mutex> lk(ctx->mu);
+		ctx->arenas.push_back(a);
+	}
+	*out = a;
+	return LZ4E_B200_OK;
+}
+
+void lz4e_b200_arena_destroy(lz4e_b200_arena *a)
+{
+	if (!a)
+		return;
+	lz4e_b200_ctx *ctx = a->ctx;
+	{
+		std::lock_guard<std::mutex> lk(ctx->mu);
+		for (size_t i = 0; i < ctx->arenas.size(); i++)
+			if (ctx->arenas[i] == a) {
+				ctx->arenas.erase(ctx->arenas.begin() + i);
+				break;
+			}
+	}
+	cudaSetDevice(ctx->device);
+	cudaFreeHost(a->host);
+	cudaFree(a->dev);
+	delete a;
+}
+
+struct page *lz4e_b200_arena_pages(lz4e_b200_arena *a) { return (struct page *)a->host; }
+void *lz4e_b200_arena_dev_base(lz4e_b200_arena *a) { return a->dev; }
+size_t lz4e_b200_arena_npages(lz4e_b200_arena *a) { return a->npages; }
+
+int lz4e_b200_arena_upload(lz4e_b200_arena *a, size_t first_page, size_t npages)
+{
+	if (first_page + npages > a->npages)
+		return LZ4E_B200_EINVAL;
+	return lz4e_b200_copy_h2d(a->ctx, nullptr, a->dev + first_page * PAGE_SIZE,
+				  a->host + first_page * PAGE_SIZE, npages * PAGE_SIZE);
+}
+
+int lz4e_b200_arena_download(lz4e_b200_arena *a, size_t first_page, size_t npages)
+{
+	if (first_page + npages > a->npages)
+		return LZ4E_B200_EINVAL;
+	return lz4e_b200_copy_d2h(a->ctx, nullptr, a->host + first_page * PAGE_SIZE,
+				  a->dev + first_page * PAGE_SIZE, npages * PAGE_SIZE);
+}
+
+uint64_t lz4e_b200_arena_translate(lz4e_b200_ctx *ctx, const void *p,
+				   lz4e_b200_arena **arena_out)
+{
+	std::lock_guard<std::mutex> lk(ctx->mu);
+
+	for (lz4e_b200_arena *a : ctx->arenas) {
+		const uint8_t *q = (const uint8_t *)p;
+
+		if (q >= a->host && q < a->host + a->npages * PAGE_SIZE) {
+			if (arena_out)
+				*arena_out = a;
+			return (uint64_t)(uintptr_t)(a->dev + (q - a->host));
+		}
+	}
+	return 0;
+}
+
+/* ---- device-level batches ------------------------------------------------ */
+static uint32_t *next_counter(lz4e_b200_ctx *ctx, cudaStream_t s)
+{
+	uint32_t *c = ctx->d_ctl + (ctx->ctl_next.fetch_add(1) % CTL_COUNTERS);
+
+	cudaMemsetAsync(c, 0, sizeof(uint32_t), s);
+	return c;
+}
+
+static int ensure_scratch(lz4e_b200_ctx *ctx, size_t bytes)
+{
+	if (bytes <= ctx->scratch_bytes)
+		return LZ4E_B200_OK;
+	CU(ctx, cudaDeviceSynchronize());
+	cudaFree(ctx->scratch);
+	ctx->scratch = nullptr;
+	ctx->scratch_bytes = 0;
+	if (cudaMalloc((void **)&ctx->scratch, bytes) != cudaSuccess) {
+		set_err(ctx, "scratch of %zu bytes: out of device memory", bytes);
+		return LZ4E_B200_ENOMEM;
+	}
+	ctx->scratch_bytes = bytes;
+	return LZ4E_B200_OK;
+}
+
+/* internal helpers for the other translation units */
+uint8_t *lz4e_ctx_scratch(lz4e_b200_ctx *ctx, size_t bytes)
+{
+	return ensure_scratch(ctx, bytes) == LZ4E_B200_OK ? ctx->scratch : nullptr;
+}
+uint32_t *lz4e_ctx_faults(lz4e_b200_ctx *ctx) { return ctx->d_ctl + CTL_FAULTS; }
+void *lz4e_ctx_stream(lz4e_b200_ctx *ctx, void *stream) { return (void *)pick(ctx, stream); }
+void lz4e_ctx_count_launches(lz4e_b200_ctx *ctx, unsigned k) { ctx->launches += k; }
+
+int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
+			   const struct lz4e_b200_dev_bvec *src_bvecs,
+			   const struct lz4e_b200_dev_iter *src_iters,
+			   const struct lz4e_b200_dev_bvec *dst_bvecs,
+			   const struct lz4e_b200_dev_iter *dst_iters,
+			   uint32_t nblocks, uint32_t max_in_bytes, uint32_t flags,
+			   int32_t *rets, struct lz4e_b200_dev_end *ends)
+{
+	lz4e_compress_args a;
+	cudaStream_t s;
+
+	if (!ctx)
+		return LZ4E_B200_ENODEV;
+	if (nblocks == 0)
+		return LZ4E_B200_OK;
+	if (max_in_bytes > 65536u) {
+		set_err(ctx, "blocks above 65536 bytes (%u) are not supported by the "
+			     "shared-memory compressor yet", max_in_bytes);
+		return LZ4E_B200_EINVAL;
+	}
+	cudaSetDevice(ctx->device);
+	s = pick(ctx, stream);
+	a.src_bvecs = src_bvecs;
+	a.src_iters = src_iters;
+	a.dst_bvecs = dst_bvecs;
+	a.dst_iters = dst_iters;
+	a.rets = rets;
+	a.ends = ends;
+	a.work_counter = next_counter(ctx, s);
+	a.faults = ctx->d_ctl + CTL_FAULTS;
+	a.nblocks = nblocks;
+	a.table_bytes = (flags & LZ4E_B200_DEV_NO_BYU16) ? 8192u : 16384u;
+	a.in_cap = (max_in_bytes + 15u) & ~15u;
+	if (a.in_cap < 16)
+		a.in_cap = 16;
+	{
+		/* whole output staged when it is small (one coalesced flush per
+		 * block), a 2 KiB streaming window otherwise */
+		const uint32_t bound = max_in_bytes + max_in_bytes / 255u + 16u;
+
+		a.out_cap = bound <= 4352u ? ((bound + 15u) & ~15u) + 16u : 2048u;
+		if (a.out_cap < 1024u)
+			a.out_cap = 1024u;
+	}
+	if (lz4e_launch_compress(&a, ctx->sm_count, s, nullptr)) {
+		set_err(ctx, "compress launch failed: %s",
+			cudaGetErrorString(cudaGetLastError()));
+		return LZ4E_B200_EIO;
+	}
+	ctx->launches++;
+	return LZ4E_B200_OK;
+}
+
+int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
+			     const struct lz4e_b200_dev_bvec *src_bvecs,
+			     const struct lz4e_b200_dev_iter *src_iters,
+			     const struct lz4e_b200_dev_bvec *dst_bvecs,
+			     const struct lz4e_b200_dev_iter *dst_iters,
+			     uint32_t nblocks, uint32_t max_in_bytes,
+			     uint32_t max_out_bytes, uint32_t flags, int32_t *rets)
+{
+	lz4e_decompress_args a;
+	cudaStream_t s;
+	int stage, grid_limit = 0;
+	const int group = ctx ? ctx->dgroup : 8;
+
+	(void)max_in_bytes;
+	if (!ctx)
+		return LZ4E_B200_ENODEV;
+	if (nblocks == 0)
+		return LZ4E_B200_OK;
+	cudaSetDevice(ctx->device);
+	s = pick(ctx, stream);
+	stage = max_out_bytes <= 4096u + 64u;
+	if (ctx->dstage == 0)
+		stage = 0;
+	a.src_bvecs = src_bvecs;
+	a.src_iters = src_iters;
+	a.dst_bvecs = dst_bvecs;
+	a.dst_iters = dst_iters;
+	a.rets = rets;
+	a.faults = ctx->d_ctl + CTL_FAULTS;
+	a.nblocks = nblocks;
+	a.stage_cap = stage ? (((max_out_bytes + 15u) & ~15u) + 16u) : 0u;
+	a.scratch = nullptr;
+	a.scratch_stride = 0;
+	if (!stage && !(flags & LZ4E_B200_DEV_DST_LINEAR)) {
+		/* one linear slot per resident group for scattered destinations */
+		const uint32_t stride = (max_out_bytes + 255u) & ~255u;
+		int grid = lz4e_decompress_max_grid(group, 0, 0, ctx->sm_count);
+		const size_t per_cta = (size_t)LZ4E_D_WARPS * (32 / group) * stride;
+		const size_t budget = (size_t)2 << 30;
+
+		if (grid < 1) {
+			set_err(ctx, "decompress occupancy query failed");
+			return LZ4E_B200_EIO;
+		}
+		if ((size_t)grid * per_cta > budget) {
+			grid = (int)(budget / per_cta);
+			if (grid < 1)
+				grid = 1;
+		}
+		grid_limit = grid;
+		int rc = ensure_scratch(ctx, (size_t)grid * per_cta);
+
+		if (rc)
+			return rc;
+		a.scratch = ctx->scratch;
+		a.scratch_stride = stride;
+	}
+	a.work_counter = next_counter(ctx, s);
+	if (lz4e_launch_decompress(&a, group, stage, ctx->sm_count, s, grid_limit, nullptr)) {
+		set_err(ctx, "decompress launch failed: %s",
+			cudaGetErrorString(cudaGetLastError()));
+		return LZ4E_B200_EIO;
+	}
+	ctx->launches++;
+	return LZ4E_B200_OK;
+}
+
+int lz4e_b200_synth_fill_dev(lz4e_b200_ctx *ctx, void *stream,
+			     const struct lz4e_b200_dev_bvec *bvecs,
+			     const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
+			     uint32_t first_index)
+{
+	/* generate into linear slots, then scatter into the SG layout; chunked so
+	 * the linear scratch stays small */
+	const uint32_t stride = 65536u; /* blocks up to 64 KiB */
+	const uint32_t chunk = 8192u;
+	cudaStream_t s;
+	int rc;
+
+	if (!ctx)
+		return LZ4E_B200_ENODEV;
+	cudaSetDevice(ctx->device);
+	s = pick(ctx, stream);
+	rc = ensure_scratch(ctx, (size_t)chunk * stride);
+	if (rc)
+		return rc;
+	for (uint32_t b0 = 0; b0 < nblocks; b0 += chunk) {
+		const uint32_t nb = nblocks - b0 < chunk ? nblocks - b0 : chunk;
+
+		ctx->launches += 2;
+		if (lz4e_launch_synth(ctx->scratch, stride, iters + b0, nb, first_index + b0, s) ||
+		    lz4e_launch_scatter(ctx->scratch, stride, bvecs, iters + b0, nb,
+					ctx->sm_count, s)) {
+			set_err(ctx, "synth launch failed: %s",
+				cudaGetErrorString(cudaGetLastError()));
+			return LZ4E_B200_EIO;
+		}
+	}
+	return LZ4E_B200_OK;
+}
+
+void lz4e_b200_synth_fill_host(uint8_t *buf, uint32_t n, uint32_t cls, uint32_t seed)
+{
+	lz4e_synth_block(buf, n, cls, seed);
+}
+
+void lz4e_b200_shard_range(uint64_t nblocks, uint32_t rank, uint32_t world,
+			   uint64_t *first, uint64_t *count)
+{
+	if (world == 0)
+		world = 1;
+	const uint64_t lo = nblocks * rank / world;
+	const uint64_t hi = nblocks * (rank + 1ull) / world;
+
+	*first = lo;
+	*count = hi - lo;
+}
+
+} /* extern "C" */

@@ -59,14 +59,16 @@ struct lz4e_compress_args {
 	uint32_t *work_counter;		/* zeroed before launch */
 	uint32_t *faults;
 	uint32_t nblocks;
+	uint32_t table_bytes; /* 16384, or 8192 when no block can select byU16 */
 	uint32_t in_cap;  /* bytes of input staging (multiple of 16) */
 	uint32_t out_cap; /* bytes of output staging (multiple of 16, >= 1024) */
 };
 
 /* shared memory needed by one warp */
-static inline uint32_t lz4e_compress_smem_bytes(uint32_t in_cap, uint32_t out_cap)
+static inline uint32_t lz4e_compress_smem_bytes(uint32_t table_bytes,
+						uint32_t in_cap, uint32_t out_cap)
 {
-	return LZ4E_K_TABLE_BYTES + in_cap + LZ4E_K_PAD + out_cap + LZ4E_K_PAD;
+	return table_bytes + in_cap + LZ4E_K_PAD + out_cap + LZ4E_K_PAD;
 }
 
 /* number of bytes advanced after k search visits: visit k uses step 1 for
@@ -142,7 +144,7 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 	const uint32_t n = si.bi_size;
 	const uint32_t cap = di.bi_size;
 	uint16_t *tab = reinterpret_cast<uint16_t *>(sm);
-	uint8_t *in_area = sm + LZ4E_K_TABLE_BYTES;
+	uint8_t *in_area = sm + a.table_bytes;
 	uint8_t *out_area = in_area + a.in_cap + LZ4E_K_PAD;
 	const uint8_t *d; /* d[pos] = source byte at linear position pos */
 	int tt = LZ4E_TT_U16;
@@ -215,6 +217,13 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 						: tt == LZ4E_TT_U32 ? 8192u
 								    : 4096u;
 			const lz4e_u128 z = { 0, 0, 0, 0 };
+
+			if (tbytes > a.table_bytes) {
+				/* launched for byU32-only batches, block wants byU16 */
+				if (lane == 0)
+					lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
+				goto done;
+			}
 
 			for (uint32_t i = lane * 16u; i < tbytes; i += 512u)
 				lz4e_st128(sm + i, z);

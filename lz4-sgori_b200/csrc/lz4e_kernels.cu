@@ -1,0 +1,203 @@
+/*
+ * lz4e_kernels.cu — __global__ entry points (sm_100a) around the warp bodies
+ * and their launch helpers.  The C ABI in lz4e_abi.cu calls the
+ * lz4e_launch_* functions declared in lz4e_kernels.h.
+ */
+#include <cuda_runtime.h>
+
+#include "lz4e_compress_body.cuh"
+#include "lz4e_decompress_body.cuh"
+#include "lz4e_kernels.h"
+#include "lz4e_synth.h"
+
+extern __shared__ __align__(16) uint8_t lz4e_smem[];
+
+/* ---- K2: compression, one warp (= one CTA) per block in flight ----------- */
+__global__ void __launch_bounds__(32)
+lz4e_compress_kernel(const lz4e_compress_args a)
+{
+	lz4e_compress_warp(a, lz4e_smem, threadIdx.x);
+}
+
+/* ---- K4: decompression, LZ4E_D_WARPS warps per CTA, 32/GS blocks per warp */
+template <int GS, bool STAGE>
+__global__ void __launch_bounds__(LZ4E_D_WARPS * 32)
+lz4e_decompress_kernel(const lz4e_decompress_args a)
+{
+	const uint32_t warp = threadIdx.x >> 5;
+	const uint32_t groups = 32 / GS;
+	uint8_t *sm = lz4e_smem + (size_t)warp * groups * (a.stage_cap + LZ4E_D_PAD);
+	const uint32_t slot0 = (blockIdx.x * LZ4E_D_WARPS + warp) * groups;
+
+	lz4e_decompress_warp_impl<GS, STAGE>(a, sm, slot0, threadIdx.x & 31);
+}
+
+/* ---- synthetic contents: one thread writes one linear block --------------- */
+__global__ void lz4e_synth_kernel(uint8_t *lin, uint32_t stride,
+				  const struct lz4e_b200_dev_iter *iters,
+				  uint32_t nblocks, uint32_t first_index)
+{
+	const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+
+	if (b >= nblocks)
+		return;
+	lz4e_synth_block(lin + (size_t)b * stride, iters[b].bi_size,
+			 (first_index + b) & 3u, first_index + b);
+}
+
+/* linear slots -> SG blocks (also used to pack compacted output), one warp
+ * per block */
+__global__ void __launch_bounds__(128)
+lz4e_scatter_kernel(const uint8_t *lin, uint32_t stride,
+		    const struct lz4e_b200_dev_bvec *bvecs,
+		    const struct lz4e_b200_dev_iter *iters, uint32_t nblocks)
+{
+	const uint32_t lane = threadIdx.x & 31;
+
+	for (uint32_t b = blockIdx.x * 4 + (threadIdx.x >> 5); b < nblocks;
+	     b += gridDim.x * 4) {
+		lz4e_cursor c = lz4e_cursor_init(bvecs, iters[b]);
+
+		lz4e_scatter<32>(c, lin + (size_t)b * stride, iters[b].bi_size, lane);
+	}
+}
+
+/* ------------------------------------------------------------------------- */
+
+static int lz4e_set_smem(const void *fn, size_t bytes)
+{
+	if (bytes <= 48 * 1024)
+		return 0;
+	return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+				    (int)bytes) == cudaSuccess
+		       ? 0
+		       : -1;
+}
+
+int lz4e_launch_compress(const lz4e_compress_args *a, int sm_count,
+			 cudaStream_t stream, int *grid_out)
+{
+	const size_t smem = lz4e_compress_smem_bytes(a->table_bytes, a->in_cap, a->out_cap);
+	int per_sm = 0;
+
+	if (lz4e_set_smem((const void *)lz4e_compress_kernel, smem))
+		return -1;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+		    &per_sm, lz4e_compress_kernel, 32, smem) != cudaSuccess ||
+	    per_sm < 1)
+		return -1;
+	long long grid = (long long)per_sm * sm_count;
+
+	if (grid > (long long)a->nblocks)
+		grid = a->nblocks;
+	if (grid < 1)
+		grid = 1;
+	lz4e_compress_kernel<<<(unsigned)grid, 32, smem, stream>>>(*a);
+	if (grid_out)
+		*grid_out = (int)grid;
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+template <int GS, bool STAGE>
+static int launch_decompress_t(const lz4e_decompress_args *a, int sm_count,
+			       cudaStream_t stream, int grid_limit, int *grid_out)
+{
+	const size_t smem =
+		STAGE ? (size_t)LZ4E_D_WARPS * (32 / GS) * (a->stage_cap + LZ4E_D_PAD) : 0;
+	int per_sm = 0;
+	auto fn = lz4e_decompress_kernel<GS, STAGE>;
+
+	if (lz4e_set_smem((const void *)fn, smem))
+		return -1;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+		    &per_sm, fn, LZ4E_D_WARPS * 32, smem) != cudaSuccess ||
+	    per_sm < 1)
+		return -1;
+	long long grid = (long long)per_sm * sm_count;
+	const long long want =
+		((long long)a->nblocks + LZ4E_D_WARPS * (32 / GS) - 1) /
+		(LZ4E_D_WARPS * (32 / GS));
+
+	if (grid > want)
+		grid = want;
+	if (grid_limit > 0 && grid > grid_limit)
+		grid = grid_limit;
+	if (grid < 1)
+		grid = 1;
+	fn<<<(unsigned)grid, LZ4E_D_WARPS * 32, smem, stream>>>(*a);
+	if (grid_out)
+		*grid_out = (int)grid;
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_count)
+{
+	int per_sm = 0;
+	size_t smem = stage ? (size_t)LZ4E_D_WARPS * (32 / group) * (stage_cap + LZ4E_D_PAD) : 0;
+	const void *fn;
+
+	if (stage)
+		fn = group == 8    ? (const void *)lz4e_decompress_kernel<8, true>
+		     : group == 16 ? (const void *)lz4e_decompress_kernel<16, true>
+				   : (const void *)lz4e_decompress_kernel<32, true>;
+	else
+		fn = group == 8    ? (const void *)lz4e_decompress_kernel<8, false>
+		     : group == 16 ? (const void *)lz4e_decompress_kernel<16, false>
+				   : (const void *)lz4e_decompress_kernel<32, false>;
+	if (lz4e_set_smem(fn, smem))
+		return -1;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, LZ4E_D_WARPS * 32,
+							  smem) != cudaSuccess ||
+	    per_sm < 1)
+		return -1;
+	return per_sm * sm_count;
+}
+
+int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
+			   int sm_count, cudaStream_t stream, int grid_limit,
+			   int *grid_out)
+{
+	if (stage) {
+		switch (group) {
+		case 8:
+			return launch_decompress_t<8, true>(a, sm_count, stream, grid_limit, grid_out);
+		case 16:
+			return launch_decompress_t<16, true>(a, sm_count, stream, grid_limit, grid_out);
+		default:
+			return launch_decompress_t<32, true>(a, sm_count, stream, grid_limit, grid_out);
+		}
+	}
+	switch (group) {
+	case 8:
+		return launch_decompress_t<8, false>(a, sm_count, stream, grid_limit, grid_out);
+	case 16:
+		return launch_decompress_t<16, false>(a, sm_count, stream, grid_limit, grid_out);
+	default:
+		return launch_decompress_t<32, false>(a, sm_count, stream, grid_limit, grid_out);
+	}
+}
+
+int lz4e_launch_synth(uint8_t *lin, uint32_t stride,
+		      const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
+		      uint32_t first_index, cudaStream_t stream)
+{
+	lz4e_synth_kernel<<<(nblocks + 63) / 64, 64, 0, stream>>>(lin, stride, iters,
+								  nblocks, first_index);
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+int lz4e_launch_scatter(const uint8_t *lin, uint32_t stride,
+			const struct lz4e_b200_dev_bvec *bvecs,
+			const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
+			int sm_count, cudaStream_t stream)
+{
+	long long grid = ((long long)nblocks + 3) / 4;
+
+	if (grid > (long long)sm_count * 16)
+		grid = (long long)sm_count * 16;
+	if (grid < 1)
+		grid = 1;
+	lz4e_scatter_kernel<<<(unsigned)grid, 128, 0, stream>>>(lin, stride, bvecs, iters,
+								nblocks);
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}

@@ -1,0 +1,29 @@
+/* lz4e_kernels.h — launch helpers implemented in lz4e_kernels.cu */
+#ifndef LZ4E_KERNELS_H
+#define LZ4E_KERNELS_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/lz4e_b200.h"
+
+#define LZ4E_D_WARPS 4 /* warps per decompression CTA */
+
+struct lz4e_compress_args;
+struct lz4e_decompress_args;
+
+int lz4e_launch_compress(const lz4e_compress_args *a, int sm_count,
+			 cudaStream_t stream, int *grid_out);
+int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_count);
+int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
+			   int sm_count, cudaStream_t stream, int grid_limit,
+			   int *grid_out);
+int lz4e_launch_synth(uint8_t *lin, uint32_t stride,
+		      const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
+		      uint32_t first_index, cudaStream_t stream);
+int lz4e_launch_scatter(const uint8_t *lin, uint32_t stride,
+			const struct lz4e_b200_dev_bvec *bvecs,
+			const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
+			int sm_count, cudaStream_t stream);
+
+#endif

@@ -194,12 +194,13 @@ int simt_compress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 			const lz4e_b200_dev_iter *src_iters,
 			const lz4e_b200_dev_bvec *dst_bvecs,
 			const lz4e_b200_dev_iter *dst_iters, uint32_t nblocks,
-			uint32_t in_cap, uint32_t out_cap, int32_t *rets,
-			lz4e_b200_dev_end *ends, uint32_t *faults, uint32_t seed)
+			uint32_t table_bytes, uint32_t in_cap, uint32_t out_cap,
+			int32_t *rets, lz4e_b200_dev_end *ends, uint32_t *faults,
+			uint32_t seed)
 {
 	lz4e_compress_args a;
 	uint32_t counter = 0;
-	const uint32_t bytes = lz4e_compress_smem_bytes(in_cap, out_cap);
+	const uint32_t bytes = lz4e_compress_smem_bytes(table_bytes, in_cap, out_cap);
 	void *smraw = nullptr;
 
 	if (posix_memalign(&smraw, 1024, bytes + 64))
@@ -214,6 +215,7 @@ int simt_compress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 	a.work_counter = &counter;
 	a.faults = faults;
 	a.nblocks = nblocks;
+	a.table_bytes = table_bytes;
 	a.in_cap = in_cap;
 	a.out_cap = out_cap;
 	uint8_t *sm = (uint8_t *)smraw;
