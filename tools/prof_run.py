@@ -1,0 +1,67 @@
+#!/usr/bin/env python
+"""tools/prof_run.py — a short, fixed sequence of launches for ncu:
+   [synth x2] compress(4 KiB) decompress(4 KiB) [synth x2] compress(64 KiB) decompress(64 KiB)
+Sizes are small so `ncu --set full` (about 40 replays per kernel) stays cheap."""
+import importlib
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+
+pkg = importlib.import_module("lz4-sgori_b200")
+
+
+def main():
+    n4 = int(sys.argv[1]) if len(sys.argv) > 1 else 32768
+    n64 = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
+    reps = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+    ctx = pkg.Context(0)
+    # ---- 4 KiB, one bvec ----
+    d_src, d_dst, d_out = ctx.dev_alloc(n4 * 4096), ctx.dev_alloc(n4 * bench.DST_STRIDE), ctx.dev_alloc(n4 * 4096)
+    (sbv, sit), (dbv, dit), (obv, oit) = bench.cfg2_tables(pkg, d_src, d_dst, d_out, n4)
+    t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
+    r1, r2 = ctx.dev_alloc(4 * n4), ctx.dev_alloc(4 * n4)
+    ctx.synth_fill_dev(t[0], t[1], n4)
+    for _ in range(reps):
+        ctx.compress_dev(t[0], t[1], t[2], t[3], n4, 4096, r1)
+    ctx.sync()
+    rets = ctx.download(r1, np.int32, n4)
+    cit = dit.copy()
+    cit["bi_size"] = rets.astype(np.uint32)
+    d_cit = ctx.upload(cit)
+    for _ in range(reps):
+        ctx.decompress_dev(t[2], d_cit, t[4], t[5], n4, int(rets.max()), 4096, r2, flags=pkg.DEV_DST_LINEAR)
+    ctx.sync()
+    assert (ctx.download(r2, np.int32, n4) == 4096).all()
+    print("4k ok", n4, int(rets.sum()))
+    # ---- 64 KiB, 16 odd segments ----
+    if n64:
+        bound = pkg.compress_bound(65536)
+        region = n64 * 16 * 3 * 4096
+        a, b, c = ctx.dev_alloc(region), ctx.dev_alloc(region), ctx.dev_alloc(region)
+        sbv, sit, _ = bench.cfg3_tables(pkg, a, n64, 65536, 65536, 0)
+        dbv, dit, _ = bench.cfg3_tables(pkg, b, n64, bound, bound, 11)
+        obv, oit, _ = bench.cfg3_tables(pkg, c, n64, 65536, 65536, 5)
+        t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
+        r1, r2 = ctx.dev_alloc(4 * n64), ctx.dev_alloc(4 * n64)
+        ctx.synth_fill_dev(t[0], t[1], n64)
+        for _ in range(reps):
+            ctx.compress_dev(t[0], t[1], t[2], t[3], n64, 65536, r1, flags=pkg.DEV_NO_BYU16)
+        ctx.sync()
+        rets = ctx.download(r1, np.int32, n64)
+        cit = dit.copy()
+        cit["bi_size"] = rets.astype(np.uint32)
+        d_cit = ctx.upload(cit)
+        for _ in range(reps):
+            ctx.decompress_dev(t[2], d_cit, t[4], t[5], n64, int(rets.max()), 65536, r2)
+        ctx.sync()
+        assert (ctx.download(r2, np.int32, n64) == 65536).all()
+        print("64k ok", n64, int(rets.sum()))
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()
