@@ -440,9 +440,14 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 		return LZ4E_B200_OK;
 	cudaSetDevice(ctx->device);
 	s = pick(ctx, stream);
-	stage = max_out_bytes <= 4096u + 64u;
+	/* small blocks with scattered destinations are built in shared memory and
+	 * flushed segment by segment; linear destinations are decoded in place
+	 * (more resident warps) */
+	stage = max_out_bytes <= 4096u + 64u && !(flags & LZ4E_B200_DEV_DST_LINEAR);
 	if (ctx->dstage == 0)
 		stage = 0;
+	if (ctx->dstage == 1 && max_out_bytes <= 4096u + 64u)
+		stage = 1;
 	a.src_bvecs = src_bvecs;
 	a.src_iters = src_iters;
 	a.dst_bvecs = dst_bvecs;

@@ -201,6 +201,8 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 		const bool limited = cap < n + n / 255u + 16u; /* :553 */
 		const uint32_t mflimit = n - 12u;
 		const uint32_t matchlimit = n - 5u;
+		/* the whole output fits the staging area: one flush at the end */
+		const bool whole = a.out_cap >= (cap < n + n / 255u + 16u ? cap : n + n / 255u + 16u);
 		uint32_t anchor = 0, op = 0;
 		lz4e_out_stage st;
 
@@ -239,18 +241,16 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 				/* ---- one speculative batch of 32 visits ---- */
 				const int k = kbase + (int)lane;
 				uint32_t pos, seq = 0, h = 0xffffffffu, m = 0;
-				bool valid, ins_only = false;
+				bool valid;
 
-				if (k == -2) {
-					pos = p0 - 3u; /* fill table at ip-2 */
-					valid = true;
-					ins_only = true;
-				} else if (k == -1) {
-					pos = p0 - 1u; /* test next position */
-					valid = true;
+				if (kbase + 31 <= 64) {
+					/* step is still 1 everywhere in this batch; lanes
+					 * -2 / -1 are the post-match table fill at ip-2 and
+					 * the "test next position" visit at ip */
+					pos = p0 + (uint32_t)k - (k == -2 ? 1u : 0u);
+					valid = k < 0 || pos + 1u <= mflimit;
 				} else {
-					const uint32_t step =
-						k == 0 ? 1u : (63u + (uint32_t)k) >> 6;
+					const uint32_t step = (63u + (uint32_t)k) >> 6;
 
 					pos = p0 + lz4e_search_advance(k);
 					valid = pos + step <= mflimit;
@@ -267,86 +267,87 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 					h = lz4e_hash(seq, (w1 >> sh) & 0xffu, tt);
 					m = tab[h];
 				}
-				{
-					const uint32_t peers = lz4e_match_any(LZ4E_FULL, h);
-					const uint32_t lower = peers & ((1u << lane) - 1u);
-					const int srcl = lower ? 31 - lz4e_clz(lower)
-							       : (int)lane;
-					const uint32_t mj = lz4e_shfl(LZ4E_FULL, pos, srcl);
-					bool ok = false;
+				const uint32_t peers = lz4e_match_any(LZ4E_FULL, h);
+				const uint32_t lower = peers & ((1u << lane) - 1u);
+				const int srcl = lower ? 31 - lz4e_clz(lower) : (int)lane;
+				const uint32_t mj = lz4e_shfl(LZ4E_FULL, pos, srcl);
+				bool ok = false;
 
-					if (lower)
-						m = mj;
-					if (valid && !ins_only && m + 65535u >= pos)
-						ok = lz4e_ld32u(d + m) == seq;
+				if (lower)
+					m = mj;
+				if (valid && k != -2 && m + 65535u >= pos)
+					ok = lz4e_ld32u(d + m) == seq;
 
-					const uint32_t okmask = lz4e_ballot(LZ4E_FULL, ok);
+				const uint32_t okmask = lz4e_ballot(LZ4E_FULL, ok);
+
+				if (okmask == 0) {
 					const uint32_t vmask = lz4e_ballot(LZ4E_FULL, valid);
 
-					if (okmask == 0) {
-						if (vmask != LZ4E_FULL) {
-							/* ran into mflimit: last literals.
-							 * *srcIter stays at the last
-							 * visited search position */
-							const int nv = lz4e_popc(vmask);
-							const int lastk = kbase + nv - 1;
+					if (vmask != LZ4E_FULL) {
+						/* ran into mflimit: last literals.  *srcIter
+						 * stays at the last visited search position */
+						const int lastk = kbase + lz4e_popc(vmask) - 1;
 
-							if (lastk >= 0)
-								src_end = p0 +
-									lz4e_search_advance(lastk);
-							else
-								src_end = p0;
+						src_end = p0 + (lastk >= 0 ? lz4e_search_advance(lastk)
+									   : 0u);
+						break;
+					}
+					/* commit all 32 visits, keep searching */
+					if ((peers >> lane) >> 1 == 0)
+						tab[h] = (uint16_t)pos;
+					lz4e_syncwarp(LZ4E_FULL);
+					kbase += 32;
+					continue;
+				}
+
+				/* ---- a match: commit visits 0..f in serial order ---- */
+				const int f = lz4e_ffs(okmask) - 1;
+
+				if ((int)lane <= f &&
+				    (peers & ((2u << f) - 1u) & ~((2u << lane) - 1u)) == 0)
+					tab[h] = (uint16_t)pos;
+
+				const uint32_t ip = lz4e_shfl(LZ4E_FULL, pos, f);
+				const uint32_t mp = lz4e_shfl(LZ4E_FULL, m, f);
+
+				/* ---- catch up (:339-349) and match length
+				 * (lz4e_defs.h:587-636): one byte per lane each way ---- */
+				uint32_t back = 0, ml;
+				{
+					const uint32_t fip = ip + 4u, fm = mp + 4u;
+					const uint32_t limit = matchlimit - fip;
+					uint32_t lim = ip - anchor;
+					bool beq = false, fne = true;
+
+					if (mp < lim)
+						lim = mp;
+					if (lane < lim)
+						beq = d[ip - 1u - lane] == d[mp - 1u - lane];
+					if (lane < limit)
+						fne = d[fip + lane] != d[fm + lane];
+					const uint32_t bne = lz4e_ballot(LZ4E_FULL, !beq);
+					const uint32_t fnz = lz4e_ballot(LZ4E_FULL, fne);
+
+					back = bne ? (uint32_t)lz4e_ffs(bne) - 1u : 32u;
+					while (bne == 0 && back < lim) { /* rare: > 32 back */
+						const uint32_t i = back + lane;
+						bool eq = false;
+
+						if (i < lim)
+							eq = d[ip - 1u - i] == d[mp - 1u - i];
+						const uint32_t ne = lz4e_ballot(LZ4E_FULL, !eq);
+
+						if (ne) {
+							back += (uint32_t)lz4e_ffs(ne) - 1u;
 							break;
 						}
-						/* commit all 32 visits, keep searching */
-						if ((peers >> lane) >> 1 == 0)
-							tab[h] = (uint16_t)pos;
-						lz4e_syncwarp(LZ4E_FULL);
-						kbase += 32;
-						continue;
+						back += 32u;
 					}
-
-					/* ---- a match: commit visits 0..f in order ---- */
-					const int f = lz4e_ffs(okmask) - 1;
-					const uint32_t upto = (2u << f) - 1u;
-					const uint32_t later =
-						peers & upto & ~((2u << lane) - 1u);
-
-					if ((int)lane <= f && later == 0)
-						tab[h] = (uint16_t)pos;
-
-					uint32_t ip = lz4e_shfl(LZ4E_FULL, pos, f);
-					uint32_t mp = lz4e_shfl(LZ4E_FULL, m, f);
-
-					/* ---- catch up (:339-349) ---- */
-					uint32_t back = 0;
-					{
-						uint32_t lim = ip - anchor;
-
-						if (mp < lim)
-							lim = mp;
-						while (back < lim) {
-							const uint32_t i = back + lane;
-							bool eq = false;
-
-							if (i < lim)
-								eq = d[ip - 1u - i] ==
-								     d[mp - 1u - i];
-							const uint32_t ne =
-								lz4e_ballot(LZ4E_FULL, !eq);
-							if (ne) {
-								back += (uint32_t)lz4e_ffs(ne) - 1u;
-								break;
-							}
-							back += 32u;
-						}
-					}
-					/* ---- match length (lz4e_defs.h:587-636) ---- */
-					uint32_t ml = 0;
-					{
-						const uint32_t fip = ip + 4u, fm = mp + 4u;
-						const uint32_t limit = matchlimit - fip;
-
+					if (fnz) {
+						ml = (uint32_t)lz4e_ffs(fnz) - 1u;
+					} else {
+						/* >= 32 equal bytes: continue 4 bytes per lane */
+						ml = 32u;
 						for (;;) {
 							const uint32_t o = ml + 4u * lane;
 							uint32_t x = 1;
@@ -369,68 +370,91 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 						if (ml > limit)
 							ml = limit;
 					}
+				}
 
-					/* ---- emit one sequence (:352-450) ---- */
-					{
-						const uint32_t lit = ip - back - anchor;
-						const uint32_t mc = back + ml;
-						const uint32_t off = ip - mp;
-						const uint32_t lit_ext =
-							lit >= 15u ? (lit - 15u) / 255u + 1u : 0u;
-						const uint32_t mc_ext =
-							mc >= 15u ? (mc - 15u) / 255u + 1u : 0u;
-						const uint32_t need =
-							1u + lit_ext + lit + 2u + mc_ext;
+				/* ---- emit one sequence (:352-450) ---- */
+				{
+					const uint32_t lit = ip - back - anchor;
+					const uint32_t mc = back + ml;
+					const uint32_t off = ip - mp;
+					uint32_t lit_ext = 0, mc_ext = 0;
 
-						if (limited &&
-						    (op + 1u + lit + 8u + lit / 255u > cap ||
-						     op + 1u + lit_ext + lit + 2u + 6u + (mc >> 8) >
-							     cap))
-							goto done; /* ret stays 0 */
+					if (lit >= 15u)
+						lit_ext = (lit - 15u) / 255u + 1u;
+					if (mc >= 15u)
+						mc_ext = (mc - 15u) / 255u + 1u;
+					const uint32_t need = 1u + lit_ext + lit + 2u + mc_ext;
 
-						if (op - st.win + need > st.cap)
-							lz4e_stage_flush(st, op, a.out_cap, lane);
-						const bool stream = op - st.win + need > st.cap;
-						uint8_t *o = st.cur0 + (op - st.win);
+					if (limited &&
+					    (op + 1u + lit + 8u + lit / 255u > cap ||
+					     op + 1u + lit_ext + lit + 2u + 6u + (mc >> 8) > cap))
+						goto done; /* ret stays 0 */
 
+					bool stream = false;
+
+					if (!whole && op - st.win + need > st.cap) {
+						lz4e_stage_flush(st, op, a.out_cap, lane);
+						stream = need > st.cap;
+					}
+					uint8_t *o = st.cur0 + (op - st.win);
+
+					if (!stream && lit < 15u && mc < 15u) {
+						/* the common short sequence: token, literals,
+						 * offset in one pass, one byte per lane */
+						uint8_t v = 0;
+
+						if (lane == 0)
+							v = (uint8_t)((lit << 4) | mc);
+						else if (lane <= lit)
+							v = d[anchor + lane - 1u];
+						else
+							v = (uint8_t)(lane == lit + 1u ? off : off >> 8);
+						if (lane < lit + 3u)
+							o[lane] = v;
+					} else {
 						if (lane == 0)
 							o[0] = (uint8_t)(((lit < 15u ? lit : 15u) << 4) |
 									 (mc < 15u ? mc : 15u));
-						lz4e_put_run(o + 1, lit_ext, (lit - 15u) % 255u, lane);
+						if (lit_ext)
+							lz4e_put_run(o + 1, lit_ext, (lit - 15u) % 255u,
+								     lane);
 						o += 1u + lit_ext;
-						op += 1u + lit_ext;
 						if (stream) {
-							/* literal run larger than the staging
-							 * area: flush the header, then stream
-							 * the literals straight from the
-							 * gathered input */
-							lz4e_stage_flush(st, op, a.out_cap, lane);
+							/* literal run larger than the staging area:
+							 * flush the header, stream the literals
+							 * straight from the gathered input */
+							lz4e_stage_flush(st, op + 1u + lit_ext, a.out_cap,
+									 lane);
 							lz4e_scatter<32>(st.dst, d + anchor, lit, lane);
-							op += lit;
-							lz4e_stage_rebase(st, op, a.out_cap);
+							lz4e_stage_rebase(st, op + 1u + lit_ext + lit,
+									  a.out_cap);
 							o = st.cur0;
 						} else {
-							lz4e_copy<32>(o, d + anchor, lit, lane);
+							if (lit <= 32u) {
+								if (lane < lit)
+									o[lane] = d[anchor + lane];
+							} else {
+								lz4e_copy<32>(o, d + anchor, lit, lane);
+							}
 							o += lit;
-							op += lit;
 						}
-						if (lane == 0) {
-							o[0] = (uint8_t)off;
-							o[1] = (uint8_t)(off >> 8);
-						}
-						lz4e_put_run(o + 2, mc_ext, (mc - 15u) % 255u, lane);
-						op += 2u + mc_ext;
+						if (lane < 2u)
+							o[lane] = (uint8_t)(lane ? off >> 8 : off);
+						if (mc_ext)
+							lz4e_put_run(o + 2, mc_ext, (mc - 15u) % 255u,
+								     lane);
 					}
-
-					anchor = ip + 4u + ml;
-					if (anchor > mflimit) { /* :456 */
-						src_end = anchor;
-						break;
-					}
-					p0 = anchor + 1u;
-					kbase = -2;
-					lz4e_syncwarp(LZ4E_FULL); /* table writes visible */
+					op += need;
 				}
+
+				anchor = ip + 4u + ml;
+				if (anchor > mflimit) { /* :456 */
+					src_end = anchor;
+					break;
+				}
+				p0 = anchor + 1u;
+				kbase = -2;
+				lz4e_syncwarp(LZ4E_FULL); /* table writes visible */
 			}
 		}
 

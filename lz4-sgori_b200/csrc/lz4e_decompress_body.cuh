@@ -120,6 +120,19 @@ LZ4E_DEV uint32_t lz4e_in_rd8(const lz4e_in_view &in, uint32_t p)
 	return lz4e_in_rd8_slow(in, p);
 }
 
+/* literal run: `len` bytes from compressed position ip to out (W lanes) */
+template <int W>
+LZ4E_DEV void lz4e_dgroup_literals(const lz4e_in_view &in, uint8_t *out,
+				   uint32_t ip, uint32_t len, uint32_t l)
+{
+	if (len >= 32u && ip + len <= in.hi) {
+		lz4e_copy<W>(out, in.bias + ip, len, l);
+		return;
+	}
+	for (uint32_t i = l; i < len; i += W)
+		out[i] = (uint8_t)lz4e_in_rd8(in, ip + i);
+}
+
 template <int GS, bool STAGE>
 struct lz4e_dgroup {
 	lz4e_in_view in;
@@ -246,6 +259,55 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 		uint32_t ip = g.ip, op = g.op;
 
 		lz4e_in_seek(g.in, ip);
+
+		/*
+		 * Fast path: a short sequence (literal length < 15, match length
+		 * < 19) whose header lies inside the current source segment and
+		 * far enough from both ends that none of the reference's
+		 * end-of-block rules can fire (the reference's own shortcut,
+		 * lz4e_decompress.c:150-191, needs ip < iend-16 and op <= oend-32;
+		 * the margins here are stricter, everything else takes the general
+		 * path below, which applies the rules one by one).
+		 */
+		{
+			const int32_t hi = (int32_t)g.in.hi < iend ? (int32_t)g.in.hi : iend;
+
+			if ((int32_t)ip < hi - 20 && (int32_t)op <= oend - 40) {
+				const uint8_t *inb = g.in.bias;
+				const uint32_t tok = inb[ip];
+				const uint32_t lit = tok >> 4, ml = tok & 15u;
+
+				if (lit != 15u && ml != 15u) {
+					const uint32_t off = (uint32_t)inb[ip + 1u + lit] |
+							     ((uint32_t)inb[ip + 2u + lit] << 8);
+
+					if (off != 0u && off <= op + lit) {
+						const uint32_t mlen = ml + 4u;
+						uint8_t *o = g.out + op;
+
+						if (gl < lit)
+							o[gl] = inb[ip + 1u + gl];
+						if (GS == 8 && gl + 8u < lit)
+							o[gl + 8u] = inb[ip + 9u + gl];
+						o += lit;
+						lz4e_syncwarp(gmask);
+						const uint8_t *ms = o - off;
+
+						if (off >= mlen) {
+							for (uint32_t i = gl; i < mlen; i += GS)
+								o[i] = ms[i];
+						} else {
+							for (uint32_t i = gl; i < mlen; i += GS)
+								o[i] = ms[i % off];
+						}
+						g.ip = ip + 3u + lit;
+						g.op = op + lit + mlen;
+						continue;
+					}
+				}
+			}
+		}
+
 		const uint32_t token = lz4e_in_rd8(g.in, ip++);
 		uint32_t len = token >> 4;
 		const bool shortcut = len != 15u && (int32_t)ip < iend - 16 &&
@@ -272,15 +334,12 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 					lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
 					continue;
 				}
-				for (uint32_t i = gl; i < len; i += GS)
-					g.out[op + i] = (uint8_t)lz4e_in_rd8(g.in, ip + i);
+				lz4e_dgroup_literals<GS>(g.in, g.out + op, ip, len, gl);
 				lz4e_dgroup_finish(a, g, (int32_t)(op + len), gmask, gl);
 				continue;
 			}
 		}
-		/* literals */
-		for (uint32_t i = gl; i < len; i += GS)
-			g.out[op + i] = (uint8_t)lz4e_in_rd8(g.in, ip + i);
+		lz4e_dgroup_literals<GS>(g.in, g.out + op, ip, len, gl);
 		ip += len;
 		op += len;
 
@@ -322,19 +381,42 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 
 		/* match: literals (and everything earlier) must be visible */
 		lz4e_syncwarp(gmask);
-		if (offset == 0u) {
-			for (uint32_t i = gl; i < mlen; i += GS)
-				g.out[op + i] = 0;
-		} else if (offset >= mlen) {
-			const uint8_t *ms = g.out + (op - offset);
+		{
+			uint8_t *o = g.out + op;
 
-			for (uint32_t i = gl; i < mlen; i += GS)
-				g.out[op + i] = ms[i];
-		} else {
-			const uint8_t *ms = g.out + (op - offset);
+			if (offset == 0u) {
+				for (uint32_t i = gl; i < mlen; i += GS)
+					o[i] = 0;
+			} else if (offset >= mlen) {
+				if (mlen >= 64u)
+					lz4e_copy<GS>(o, o - offset, mlen, gl);
+				else
+					for (uint32_t i = gl; i < mlen; i += GS)
+						o[i] = (o - offset)[i];
+			} else if (mlen < 96u) {
+				const uint8_t *ms = o - offset;
 
-			for (uint32_t i = gl; i < mlen; i += GS)
-				g.out[op + i] = ms[i % offset];
+				for (uint32_t i = gl; i < mlen; i += GS)
+					o[i] = ms[i % offset];
+			} else {
+				/* long overlapping match = a pattern of period `offset`:
+				 * write whole periods byte-wise until at least 32 bytes
+				 * exist, then keep doubling with vector copies */
+				const uint8_t *ms = o - offset;
+				uint32_t have = offset * ((31u + offset) / offset);
+
+				for (uint32_t i = gl; i < have; i += GS)
+					o[i] = ms[i % offset];
+				while (have < mlen) {
+					uint32_t chunk = mlen - have;
+
+					if (chunk > have)
+						chunk = have;
+					lz4e_syncwarp(gmask);
+					lz4e_copy<GS>(o + have, o, chunk, gl);
+					have += chunk;
+				}
+			}
 		}
 		op += mlen;
 		g.ip = ip;

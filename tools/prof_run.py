@@ -5,6 +5,7 @@ Sizes are small so `ncu --set full` (about 40 replays per kernel) stays cheap.""
 import importlib
 import os
 import sys
+import time
 
 import numpy as np
 
@@ -25,18 +26,23 @@ def main():
     t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
     r1, r2 = ctx.dev_alloc(4 * n4), ctx.dev_alloc(4 * n4)
     ctx.synth_fill_dev(t[0], t[1], n4)
+    t0 = time.perf_counter()
     for _ in range(reps):
         ctx.compress_dev(t[0], t[1], t[2], t[3], n4, 4096, r1)
     ctx.sync()
+    tc = (time.perf_counter() - t0) / reps
     rets = ctx.download(r1, np.int32, n4)
     cit = dit.copy()
     cit["bi_size"] = rets.astype(np.uint32)
     d_cit = ctx.upload(cit)
+    t0 = time.perf_counter()
     for _ in range(reps):
         ctx.decompress_dev(t[2], d_cit, t[4], t[5], n4, int(rets.max()), 4096, r2, flags=pkg.DEV_DST_LINEAR)
     ctx.sync()
+    td = (time.perf_counter() - t0) / reps
     assert (ctx.download(r2, np.int32, n4) == 4096).all()
-    print("4k ok", n4, int(rets.sum()))
+    print("4k ok", n4, int(rets.sum()), "compress %.2f GB/s  decompress %.2f GB/s (wall, incl. launch)" %
+          (n4 * 4096 / tc / 1e9, n4 * 4096 / td / 1e9))
     # ---- 64 KiB, 16 odd segments ----
     if n64:
         bound = pkg.compress_bound(65536)
@@ -48,18 +54,23 @@ def main():
         t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
         r1, r2 = ctx.dev_alloc(4 * n64), ctx.dev_alloc(4 * n64)
         ctx.synth_fill_dev(t[0], t[1], n64)
+        t0 = time.perf_counter()
         for _ in range(reps):
             ctx.compress_dev(t[0], t[1], t[2], t[3], n64, 65536, r1, flags=pkg.DEV_NO_BYU16)
         ctx.sync()
+        tc = (time.perf_counter() - t0) / reps
         rets = ctx.download(r1, np.int32, n64)
         cit = dit.copy()
         cit["bi_size"] = rets.astype(np.uint32)
         d_cit = ctx.upload(cit)
+        t0 = time.perf_counter()
         for _ in range(reps):
             ctx.decompress_dev(t[2], d_cit, t[4], t[5], n64, int(rets.max()), 65536, r2)
         ctx.sync()
+        td = (time.perf_counter() - t0) / reps
         assert (ctx.download(r2, np.int32, n64) == 65536).all()
-        print("64k ok", n64, int(rets.sum()))
+        print("64k ok", n64, int(rets.sum()), "compress %.2f GB/s  decompress %.2f GB/s (wall, incl. launch)" %
+              (n64 * 65536 / tc / 1e9, n64 * 65536 / td / 1e9))
     ctx.close()
 
 
