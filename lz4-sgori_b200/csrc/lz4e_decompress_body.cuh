@@ -133,6 +133,55 @@ LZ4E_DEV void lz4e_dgroup_literals(const lz4e_in_view &in, uint8_t *out,
 		out[i] = (uint8_t)lz4e_in_rd8(in, ip + i);
 }
 
+#define LZ4E_P_LIT 1u
+#define LZ4E_P_MATCH 2u
+#define LZ4E_P_FINISH 4u
+#define LZ4E_D_WIDE 128u /* copies of at least this many bytes go to the warp */
+#ifndef LZ4E_D_SERVICE
+#define LZ4E_D_SERVICE 0 /* 1: long copies are served by all 32 lanes of the warp */
+#endif
+
+LZ4E_DEV uint64_t lz4e_shfl64(uint64_t v, int src)
+{
+	const uint32_t lo = lz4e_shfl(LZ4E_FULL, (uint32_t)v, src);
+	const uint32_t hi = lz4e_shfl(LZ4E_FULL, (uint32_t)(v >> 32), src);
+
+	return ((uint64_t)hi << 32) | lo;
+}
+
+/* match copy by all 32 lanes: o[i] = o[i - dist]; dist == 0 writes zeros
+ * (lz4e_decompress.c:309-314).  An overlapping match is a pattern of period
+ * dist: whole periods are written byte-wise until >= 64 bytes exist, then the
+ * finished part is doubled with vector copies. */
+LZ4E_DEV void lz4e_wide_match(uint8_t *o, uint32_t dist, uint32_t len, uint32_t lane)
+{
+	if (dist == 0u) {
+		for (uint32_t i = lane; i < len; i += 32u)
+			o[i] = 0;
+		return;
+	}
+	if (dist >= len) {
+		lz4e_copy<32>(o, o - dist, len, lane);
+		return;
+	}
+	const uint8_t *ms = o - dist;
+	uint32_t have = dist * ((63u + dist) / dist);
+
+	if (have > len)
+		have = len;
+	for (uint32_t i = lane; i < have; i += 32u)
+		o[i] = ms[i % dist];
+	while (have < len) {
+		uint32_t chunk = len - have;
+
+		if (chunk > have)
+			chunk = have;
+		lz4e_syncwarp(LZ4E_FULL);
+		lz4e_copy<32>(o + have, o, chunk, lane);
+		have += chunk;
+	}
+}
+
 template <int GS, bool STAGE>
 struct lz4e_dgroup {
 	lz4e_in_view in;
@@ -142,6 +191,13 @@ struct lz4e_dgroup {
 	int32_t oend;	/* output capacity */
 	uint32_t ip, op;
 	bool active;	/* a block is being decoded */
+	bool done;	/* the batch has no more blocks for this group */
+	/* long copies handed to the whole warp (see lz4e_dwarp_service) */
+	uint32_t pend;	/* LZ4E_P_LIT | LZ4E_P_MATCH | LZ4E_P_FINISH */
+	const uint8_t *p_lsrc;
+	uint32_t p_lop, p_llen;		/* literals: out + p_lop <- p_lsrc */
+	uint32_t p_mop, p_mdist, p_mlen; /* match: out + p_mop, distance, length */
+	int32_t p_ret;
 	bool scatter;	/* !STAGE: output sits in scratch, scatter when done */
 };
 
@@ -181,7 +237,70 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 
 	g.active = false;
 	g.scatter = false;
+	g.done = false;
+	g.pend = 0;
+	g.p_lsrc = 0;
+	g.p_lop = g.p_llen = g.p_mop = g.p_mdist = g.p_mlen = 0;
+	g.p_ret = 0;
 	for (;;) {
+		/*
+		 * Every iteration starts with a full-warp vote.  It ends the loop
+		 * when all groups have run out of blocks and, just as important,
+		 * it makes the 32/GS groups of the warp RECONVERGE once per
+		 * sequence: they then issue the (branch-free) fast path together,
+		 * one instruction stream for 32/GS blocks.  Groups that are done
+		 * keep voting until the others finish.
+		 */
+		if (lz4e_ballot(LZ4E_FULL, !g.done) == 0)
+			break;
+		/*
+		 * Long literal runs and long matches are not copied by the 8/16
+		 * lanes of their group: the group posts them and ALL 32 lanes of
+		 * the warp (groups that are idle included) move them here with
+		 * 16-byte vectors.
+		 */
+		if (LZ4E_D_SERVICE) {
+			uint32_t pm = lz4e_ballot(LZ4E_FULL, g.pend != 0u && gl == 0u);
+
+			if (pm) {
+				lz4e_syncwarp(LZ4E_FULL); /* group-written bytes visible */
+				do {
+					const int L = lz4e_ffs(pm) - 1;
+					uint8_t *out = (uint8_t *)(uintptr_t)lz4e_shfl64(
+						(uint64_t)(uintptr_t)g.out, L);
+					const uint8_t *lsrc = (const uint8_t *)(uintptr_t)lz4e_shfl64(
+						(uint64_t)(uintptr_t)g.p_lsrc, L);
+					const uint32_t what = lz4e_shfl(LZ4E_FULL, g.pend, L);
+					const uint32_t lop = lz4e_shfl(LZ4E_FULL, g.p_lop, L);
+					const uint32_t llen = lz4e_shfl(LZ4E_FULL, g.p_llen, L);
+					const uint32_t mop = lz4e_shfl(LZ4E_FULL, g.p_mop, L);
+					const uint32_t mdist = lz4e_shfl(LZ4E_FULL, g.p_mdist, L);
+					const uint32_t mlen = lz4e_shfl(LZ4E_FULL, g.p_mlen, L);
+
+					if (!STAGE)
+						LZ4E_ASSUME_GLOBAL(out);
+					if (what & LZ4E_P_LIT) {
+						LZ4E_ASSUME_GLOBAL(lsrc);
+						lz4e_copy<32>(out + lop, lsrc, llen, lane);
+					}
+					if (what & LZ4E_P_MATCH) {
+						lz4e_syncwarp(LZ4E_FULL);
+						lz4e_wide_match(out + mop, mdist, mlen, lane);
+					}
+					pm &= pm - 1u;
+				} while (pm);
+				lz4e_syncwarp(LZ4E_FULL);
+			}
+			if (g.pend) {
+				const uint32_t what = g.pend;
+
+				g.pend = 0;
+				if (what & LZ4E_P_FINISH)
+					lz4e_dgroup_finish(a, g, g.p_ret, gmask, gl);
+			}
+		}
+		if (g.done)
+			continue;
 		if (!g.active) {
 			/* ---- next block for this group ---- */
 			uint32_t b = 0;
@@ -189,8 +308,10 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 			if (gl == 0)
 				b = lz4e_atomic_add(a.work_counter, 1u);
 			b = lz4e_shfl(gmask, b, gleader);
-			if (b >= a.nblocks)
-				break;
+			if (b >= a.nblocks) {
+				g.done = true;
+				continue;
+			}
 			const struct lz4e_b200_dev_iter si = a.src_iters[b];
 			const struct lz4e_b200_dev_iter di = a.dst_iters[b];
 
@@ -261,46 +382,73 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 		lz4e_in_seek(g.in, ip);
 
 		/*
-		 * Fast path: a short sequence (literal length < 15, match length
-		 * < 19) whose header lies inside the current source segment and
-		 * far enough from both ends that none of the reference's
-		 * end-of-block rules can fire (the reference's own shortcut,
-		 * lz4e_decompress.c:150-191, needs ip < iend-16 and op <= oend-32;
-		 * the margins here are stricter, everything else takes the general
-		 * path below, which applies the rules one by one).
+		 * Common path: a sequence with at most one extension byte per
+		 * length (literals < 270, match < 274 bytes) that lies inside the
+		 * current source segment and far enough from both ends that none of
+		 * the reference's end-of-block rules can fire:
+		 *   next ip <= iend - 12  rules out the input checks at
+		 *                         lz4e_decompress.c:197-200, :226-227, :322
+		 *   op + lit + mlen <= oend - 12  rules out :226, :425-431
+		 * so the shortcut predicate of :150-156 makes no difference here
+		 * and the sequence is just "copy literals, copy match".  All groups
+		 * of the warp run this path together; anything else (long runs,
+		 * block tail, segment crossings, malformed input) takes the general
+		 * path below, which applies the rules one by one.
 		 */
 		{
 			const int32_t hi = (int32_t)g.in.hi < iend ? (int32_t)g.in.hi : iend;
+			const uint8_t *inb = g.in.bias;
 
-			if ((int32_t)ip < hi - 20 && (int32_t)op <= oend - 40) {
-				const uint8_t *inb = g.in.bias;
+			if ((int32_t)ip + 4 <= hi) {
 				const uint32_t tok = inb[ip];
-				const uint32_t lit = tok >> 4, ml = tok & 15u;
+				const uint32_t e1 = inb[ip + 1u];
+				const uint32_t lext = (tok >> 4) == 15u;
+				const uint32_t lit = (tok >> 4) + (lext ? e1 : 0u);
+				const uint32_t lp = ip + 1u + lext; /* first literal */
+				const uint32_t fp = lp + lit;	     /* offset field */
 
-				if (lit != 15u && ml != 15u) {
-					const uint32_t off = (uint32_t)inb[ip + 1u + lit] |
-							     ((uint32_t)inb[ip + 2u + lit] << 8);
+				if (!(lext && e1 == 255u) && (int32_t)fp + 15 <= hi) {
+					const uint32_t off = (uint32_t)inb[fp] |
+							     ((uint32_t)inb[fp + 1u] << 8);
+					const uint32_t e2 = inb[fp + 2u];
+					const uint32_t mext = (tok & 15u) == 15u;
+					const uint32_t mlen = (tok & 15u) + 4u + (mext ? e2 : 0u);
+					const uint32_t nip = fp + 2u + mext;
 
-					if (off != 0u && off <= op + lit) {
-						const uint32_t mlen = ml + 4u;
+					if (!(mext && e2 == 255u) && off != 0u && off <= op + lit &&
+					    lit < LZ4E_D_WIDE && mlen < LZ4E_D_WIDE &&
+					    (int64_t)op + lit + mlen <= (int64_t)oend - 12) {
 						uint8_t *o = g.out + op;
 
-						if (gl < lit)
-							o[gl] = inb[ip + 1u + gl];
-						if (GS == 8 && gl + 8u < lit)
-							o[gl + 8u] = inb[ip + 9u + gl];
+						for (uint32_t i = gl; i < lit; i += GS)
+							o[i] = inb[lp + i];
 						o += lit;
-						lz4e_syncwarp(gmask);
 						const uint8_t *ms = o - off;
 
-						if (off >= mlen) {
-							for (uint32_t i = gl; i < mlen; i += GS)
-								o[i] = ms[i];
-						} else {
-							for (uint32_t i = gl; i < mlen; i += GS)
-								o[i] = ms[i % off];
+						/*
+						 * Steps of GS bytes with a group barrier in
+						 * between.  With offset >= GS (or no overlap)
+						 * each step reads bytes that were final before
+						 * it started; a shorter offset is a pattern of
+						 * period `off`, read at (i mod off) with the
+						 * index kept incrementally.
+						 */
+						uint32_t j = gl, dj = GS, wrap = 0xffffffffu;
+
+						if (off < (uint32_t)GS && off < mlen) {
+							j = gl % off;
+							dj = (uint32_t)GS % off;
+							wrap = off;
 						}
-						g.ip = ip + 3u + lit;
+						for (uint32_t i0 = 0; i0 < mlen; i0 += GS) {
+							lz4e_syncwarp(gmask);
+							if (i0 + gl < mlen)
+								o[i0 + gl] = ms[j];
+							j += dj;
+							if (j >= wrap)
+								j -= wrap;
+						}
+						g.ip = nip;
 						g.op = op + lit + mlen;
 						continue;
 					}
@@ -334,12 +482,29 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 					lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
 					continue;
 				}
+				if (LZ4E_D_SERVICE && len >= LZ4E_D_WIDE && ip + len <= g.in.hi) {
+					/* the whole warp copies, then the block ends */
+					g.pend = LZ4E_P_LIT | LZ4E_P_FINISH;
+					g.p_lsrc = g.in.bias + ip;
+					g.p_lop = op;
+					g.p_llen = len;
+					g.p_ret = (int32_t)(op + len);
+					continue;
+				}
 				lz4e_dgroup_literals<GS>(g.in, g.out + op, ip, len, gl);
 				lz4e_dgroup_finish(a, g, (int32_t)(op + len), gmask, gl);
 				continue;
 			}
 		}
-		lz4e_dgroup_literals<GS>(g.in, g.out + op, ip, len, gl);
+		const bool wide_lit = LZ4E_D_SERVICE && len >= LZ4E_D_WIDE && ip + len <= g.in.hi;
+
+		if (wide_lit) {
+			g.p_lsrc = g.in.bias + ip;
+			g.p_lop = op;
+			g.p_llen = len;
+		} else {
+			lz4e_dgroup_literals<GS>(g.in, g.out + op, ip, len, gl);
+		}
 		ip += len;
 		op += len;
 
@@ -379,6 +544,16 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 			continue;
 		}
 
+		if (wide_lit || (LZ4E_D_SERVICE && mlen >= LZ4E_D_WIDE)) {
+			/* literals first, then the match, by all 32 lanes */
+			g.pend = (wide_lit ? LZ4E_P_LIT : 0u) | LZ4E_P_MATCH;
+			g.p_mop = op;
+			g.p_mdist = offset;
+			g.p_mlen = mlen;
+			g.ip = ip;
+			g.op = op + mlen;
+			continue;
+		}
 		/* match: literals (and everything earlier) must be visible */
 		lz4e_syncwarp(gmask);
 		{

@@ -26,6 +26,8 @@ def main():
     t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
     r1, r2 = ctx.dev_alloc(4 * n4), ctx.dev_alloc(4 * n4)
     ctx.synth_fill_dev(t[0], t[1], n4)
+    ctx.compress_dev(t[0], t[1], t[2], t[3], n4, 4096, r1)
+    ctx.sync()
     t0 = time.perf_counter()
     for _ in range(reps):
         ctx.compress_dev(t[0], t[1], t[2], t[3], n4, 4096, r1)
@@ -35,6 +37,8 @@ def main():
     cit = dit.copy()
     cit["bi_size"] = rets.astype(np.uint32)
     d_cit = ctx.upload(cit)
+    ctx.decompress_dev(t[2], d_cit, t[4], t[5], n4, int(rets.max()), 4096, r2, flags=pkg.DEV_DST_LINEAR)
+    ctx.sync()
     t0 = time.perf_counter()
     for _ in range(reps):
         ctx.decompress_dev(t[2], d_cit, t[4], t[5], n4, int(rets.max()), 4096, r2, flags=pkg.DEV_DST_LINEAR)
@@ -54,6 +58,8 @@ def main():
         t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
         r1, r2 = ctx.dev_alloc(4 * n64), ctx.dev_alloc(4 * n64)
         ctx.synth_fill_dev(t[0], t[1], n64)
+        ctx.compress_dev(t[0], t[1], t[2], t[3], n64, 65536, r1, flags=pkg.DEV_NO_BYU16)
+        ctx.sync()
         t0 = time.perf_counter()
         for _ in range(reps):
             ctx.compress_dev(t[0], t[1], t[2], t[3], n64, 65536, r1, flags=pkg.DEV_NO_BYU16)
@@ -63,6 +69,8 @@ def main():
         cit = dit.copy()
         cit["bi_size"] = rets.astype(np.uint32)
         d_cit = ctx.upload(cit)
+        ctx.decompress_dev(t[2], d_cit, t[4], t[5], n64, int(rets.max()), 65536, r2)
+        ctx.sync()
         t0 = time.perf_counter()
         for _ in range(reps):
             ctx.decompress_dev(t[2], d_cit, t[4], t[5], n64, int(rets.max()), 65536, r2)
