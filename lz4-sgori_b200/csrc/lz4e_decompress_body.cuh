@@ -299,8 +299,14 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 					lz4e_dgroup_finish(a, g, g.p_ret, gmask, gl);
 			}
 		}
+		/* what this group asks the uniform copy phase below to do */
+		uint32_t c_lit = 0, c_mlen = 0, c_off = 1;
+		const uint8_t *c_lsrc = nullptr;
+		uint8_t *c_o = nullptr;
+
+		do { /* one group step; `break` leaves it */
 		if (g.done)
-			continue;
+			break;
 		if (!g.active) {
 			/* ---- next block for this group ---- */
 			uint32_t b = 0;
@@ -310,7 +316,7 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 			b = lz4e_shfl(gmask, b, gleader);
 			if (b >= a.nblocks) {
 				g.done = true;
-				continue;
+				break;
 			}
 			const struct lz4e_b200_dev_iter si = a.src_iters[b];
 			const struct lz4e_b200_dev_iter di = a.dst_iters[b];
@@ -328,7 +334,7 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 					a.rets[b] = -1;
 				}
 				g.active = false;
-				continue;
+				break;
 			}
 			/* special cases, lz4e_decompress.c:113-120 */
 			if (g.oend == 0 || g.iend == 0) {
@@ -341,7 +347,7 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 				if (gl == 0)
 					a.rets[b] = r;
 				g.active = false;
-				continue;
+				break;
 			}
 			lz4e_in_open(g.in, a.src_bvecs, si);
 			const struct lz4e_b200_dev_bvec *dv =
@@ -365,7 +371,7 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 							a.rets[b] = -1;
 						}
 						g.active = false;
-						continue;
+						break;
 					}
 					g.out = a.scratch + (size_t)(slot0 + gi) *
 								    a.scratch_stride;
@@ -418,39 +424,14 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 					if (!(mext && e2 == 255u) && off != 0u && off <= op + lit &&
 					    lit < LZ4E_D_WIDE && mlen < LZ4E_D_WIDE &&
 					    (int64_t)op + lit + mlen <= (int64_t)oend - 12) {
-						uint8_t *o = g.out + op;
-
-						for (uint32_t i = gl; i < lit; i += GS)
-							o[i] = inb[lp + i];
-						o += lit;
-						const uint8_t *ms = o - off;
-
-						/*
-						 * Steps of GS bytes with a group barrier in
-						 * between.  With offset >= GS (or no overlap)
-						 * each step reads bytes that were final before
-						 * it started; a shorter offset is a pattern of
-						 * period `off`, read at (i mod off) with the
-						 * index kept incrementally.
-						 */
-						uint32_t j = gl, dj = GS, wrap = 0xffffffffu;
-
-						if (off < (uint32_t)GS && off < mlen) {
-							j = gl % off;
-							dj = (uint32_t)GS % off;
-							wrap = off;
-						}
-						for (uint32_t i0 = 0; i0 < mlen; i0 += GS) {
-							lz4e_syncwarp(gmask);
-							if (i0 + gl < mlen)
-								o[i0 + gl] = ms[j];
-							j += dj;
-							if (j >= wrap)
-								j -= wrap;
-						}
+						c_o = g.out + op;
+						c_lsrc = inb + lp;
+						c_lit = lit;
+						c_off = off;
+						c_mlen = mlen;
 						g.ip = nip;
 						g.op = op + lit + mlen;
-						continue;
+						break;
 					}
 				}
 			}
@@ -467,7 +448,7 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 
 				if ((int32_t)ip >= iend - 15) {
 					lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
-					continue;
+					break;
 				}
 				do {
 					s = lz4e_in_rd8(g.in, ip++);
@@ -480,7 +461,7 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 				if ((int64_t)ip + len != (int64_t)iend ||
 				    (int64_t)op + len > (int64_t)oend) {
 					lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
-					continue;
+					break;
 				}
 				if (LZ4E_D_SERVICE && len >= LZ4E_D_WIDE && ip + len <= g.in.hi) {
 					/* the whole warp copies, then the block ends */
@@ -489,11 +470,11 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 					g.p_lop = op;
 					g.p_llen = len;
 					g.p_ret = (int32_t)(op + len);
-					continue;
+					break;
 				}
 				lz4e_dgroup_literals<GS>(g.in, g.out + op, ip, len, gl);
 				lz4e_dgroup_finish(a, g, (int32_t)(op + len), gmask, gl);
-				continue;
+				break;
 			}
 		}
 		const bool wide_lit = LZ4E_D_SERVICE && len >= LZ4E_D_WIDE && ip + len <= g.in.hi;
@@ -516,7 +497,7 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 		ip += 2;
 		if (offset > op) { /* :299-302 */
 			lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
-			continue;
+			break;
 		}
 		const bool full_shortcut = shortcut && mlen != 15u && offset >= 8u;
 
@@ -534,14 +515,14 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 			} while (s == 255u);
 			if (bad) {
 				lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
-				continue;
+				break;
 			}
 		}
 		mlen += 4u;
 		if (!full_shortcut &&
 		    (int64_t)op + mlen > (int64_t)oend - 5) { /* :420-431 */
 			lz4e_dgroup_finish(a, g, -(int32_t)ip - 1, gmask, gl);
-			continue;
+			break;
 		}
 
 		if (wide_lit || (LZ4E_D_SERVICE && mlen >= LZ4E_D_WIDE)) {
@@ -552,7 +533,7 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 			g.p_mlen = mlen;
 			g.ip = ip;
 			g.op = op + mlen;
-			continue;
+			break;
 		}
 		/* match: literals (and everything earlier) must be visible */
 		lz4e_syncwarp(gmask);
@@ -596,6 +577,54 @@ LZ4E_DEV void lz4e_decompress_warp_impl(const lz4e_decompress_args &a,
 		op += mlen;
 		g.ip = ip;
 		g.op = op;
+		} while (0);
+
+		/*
+		 * ---- uniform copy phase: executed by all 32 lanes together ----
+		 * Literals, then the match in steps of GS bytes.  The barriers are
+		 * full-warp ones (one cheap instruction; a per-group mask would
+		 * cost a MATCH/vote sequence each time), so every lane runs the
+		 * same number of steps: the maximum over the warp's groups.
+		 * With offset >= GS (or no overlap) each step reads bytes that
+		 * were final before it started; a shorter offset is a pattern of
+		 * period c_off, read at (i mod c_off) with the index kept
+		 * incrementally.
+		 */
+		for (uint32_t i = gl; i < c_lit; i += GS)
+			c_o[i] = c_lsrc[i];
+		{
+			uint8_t *o = c_o + c_lit;
+			const uint8_t *ms = o - c_off;
+
+			if (lz4e_ballot(LZ4E_FULL, c_off < c_mlen) == 0) {
+				/* no group has an overlapping match: one barrier (the
+				 * literals just written may be the source), then every
+				 * lane copies its bytes independently */
+				lz4e_syncwarp(LZ4E_FULL);
+				for (uint32_t i = gl; i < c_mlen; i += GS)
+					o[i] = ms[i];
+			} else {
+				const uint32_t steps = (c_mlen + (uint32_t)GS - 1u) / (uint32_t)GS;
+				const uint32_t maxsteps = lz4e_reduce_max(LZ4E_FULL, steps);
+				uint32_t j = gl, dj = GS, wrap = 0xffffffffu;
+
+				if (c_off < (uint32_t)GS && c_off < c_mlen) {
+					j = gl % c_off;
+					dj = (uint32_t)GS % c_off;
+					wrap = c_off;
+				}
+				for (uint32_t st = 0; st < maxsteps; st++) {
+					const uint32_t i = st * (uint32_t)GS + gl;
+
+					lz4e_syncwarp(LZ4E_FULL);
+					if (i < c_mlen)
+						o[i] = ms[j];
+					j += dj;
+					if (j >= wrap)
+						j -= wrap;
+				}
+			}
+		}
 	}
 }
 

@@ -38,6 +38,10 @@ LZ4E_DEV void lz4e_syncwarp(uint32_t mask)
 {
 	__syncwarp(mask);
 }
+LZ4E_DEV uint32_t lz4e_reduce_max(uint32_t mask, uint32_t v)
+{
+	return __reduce_max_sync(mask, v);
+}
 LZ4E_DEV uint32_t lz4e_funnel_r(uint32_t lo, uint32_t hi, uint32_t sh)
 {
 	return __funnelshift_r(lo, hi, sh);

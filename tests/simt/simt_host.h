@@ -22,7 +22,7 @@
 
 namespace simt
 {
-enum Op { OP_SYNC = 0, OP_BALLOT, OP_SHFL, OP_MATCH };
+enum Op { OP_SYNC = 0, OP_BALLOT, OP_SHFL, OP_MATCH, OP_REDMAX };
 uint32_t collective(Op op, uint32_t mask, uint32_t val, int src);
 } // namespace simt
 
@@ -37,6 +37,10 @@ LZ4E_DEV uint32_t lz4e_shfl(uint32_t mask, uint32_t v, int src)
 LZ4E_DEV uint32_t lz4e_match_any(uint32_t mask, uint32_t v)
 {
 	return simt::collective(simt::OP_MATCH, mask, v, 0);
+}
+LZ4E_DEV uint32_t lz4e_reduce_max(uint32_t mask, uint32_t v)
+{
+	return simt::collective(simt::OP_REDMAX, mask, v, 0);
 }
 LZ4E_DEV void lz4e_syncwarp(uint32_t mask)
 {

@@ -109,6 +109,15 @@ static void resolve(Warp *w)
 					die("shfl from a lane outside the mask");
 				w->result[j] = w->val[w->src[j]];
 				break;
+			case OP_REDMAX: {
+				uint32_t r = 0;
+
+				for (int q = 0; q < 32; q++)
+					if (((m >> q) & 1u) && w->val[q] > r)
+						r = w->val[q];
+				w->result[j] = r;
+				break;
+			}
 			case OP_MATCH: {
 				uint32_t r = 0;
 
