@@ -1,0 +1,91 @@
+"""CPU tests of the CUDA kernel BODIES (lz4e_compress_body.cuh / lz4e_decompress_body.cuh)
+compiled for the host against the 32-lane warp emulator in tests/simt — the very source
+nvcc builds — compared with the oracle.  Small sizes: the emulator is slow."""
+import numpy as np
+import pytest
+
+import common
+import emu
+from common import sg
+
+
+@pytest.fixture(scope="module")
+def simt():
+    return emu.load()
+
+
+def _host_layout(specs, datas=None):
+    return common.build_layout(sg.HostArena, specs, datas)
+
+
+def _cases():
+    rng = np.random.default_rng(7)
+    datas, specs = [], []
+    for b in range(8):  # config-2 shape
+        datas.append(common.synth(4096, b & 3, b))
+        specs.append(sg.segs_single(4096))
+    for n in (0, 1, 12, 13, 14, 64, 300, 1500):  # short inputs, lz4e_compress.c:268-271
+        datas.append(common.synth(n, 3, 50 + n) if n else np.zeros(0, np.uint8))
+        specs.append(sg.segs_single(n))
+    datas.append(common.lcg_text(9000))  # > 4096 in one bvec: byU32
+    specs.append(sg.segs_single(9000))
+    datas.append(np.zeros(5000, np.uint8))  # long RLE match
+    specs.append(sg.segs_single(5000))
+    for b in range(4):  # odd segments, mid-bvec start
+        n = int(rng.integers(2000, 12000))
+        datas.append(common.synth(n, (b + 1) & 3, 900 + b))
+        specs.append(sg.segs_odd(n, int(rng.integers(2, 9)), b))
+    return datas, specs
+
+
+def test_compress_body_matches_oracle(simt, ref_lib):
+    datas, specs = _cases()
+    src = _host_layout(specs, datas)
+    dspecs = [sg.segs_single(sg.compress_bound(len(d))) for d in datas]
+    dst = _host_layout(dspecs)
+    dst.arena.mem[:] = 0xEE
+    rets, ends, faults = emu.compress(simt, src, dst, in_cap=12288, out_cap=1024)
+    ref_dst, (ref_rets, _, so, do) = common.oracle_compress(ref_lib, src, dspecs, want_iters=True)
+    assert faults == 0
+    assert np.array_equal(rets, ref_rets)
+    for b in range(len(datas)):
+        assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
+        if rets[b] > 0:
+            assert int(ends[b]["src_pos"]) == len(datas[b]) - int(so[b]["bi_size"]), b
+            assert int(ends[b]["dst_pos"]) == int(dspecs[b]["size"]) - int(do[b]["bi_size"]), b
+
+
+def test_compress_body_limited_output(simt, ref_lib):
+    datas = [common.synth(4096, c, 77 + c) for c in range(4)] * 3
+    specs = [sg.segs_single(4096)] * len(datas)
+    src = _host_layout(specs, datas)
+    full = _host_layout([sg.segs_single(sg.compress_bound(4096))] * len(datas))
+    sizes, _ = common.oracle.compress_batch(ref_lib, src.bvecs, src.first, src.iters,
+                                            full.bvecs, full.first, full.iters)
+    caps = [int(s) + d for s, d in zip(sizes, [0, -1, -7, 5] * 3)]  # exact fit, too small, ...
+    dspecs = [sg.segs_single(max(c, 1)) for c in caps]
+    dst = _host_layout(dspecs)
+    rets, _, faults = emu.compress(simt, src, dst, in_cap=4096, out_cap=1024)
+    ref_dst, (ref_rets, _) = common.oracle_compress(ref_lib, src, dspecs)
+    assert faults == 0
+    assert np.array_equal(rets, ref_rets)
+    for b in range(len(datas)):
+        assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
+
+
+@pytest.mark.parametrize("group", [8, 16, 32])
+def test_decompress_body_roundtrip(simt, ref_lib, group):
+    datas, specs = _cases()
+    keep = [i for i, d in enumerate(datas) if len(d) > 0]
+    datas, specs = [datas[i] for i in keep], [specs[i] for i in keep]
+    src = _host_layout(specs, datas)
+    dspecs = [sg.segs_single(sg.compress_bound(len(d))) for d in datas]
+    cdst, (sizes, _) = common.oracle_compress(ref_lib, src, dspecs)
+    out = _host_layout([sg.segs_single(len(d)) for d in datas])
+    csrc = sg.Layout(cdst.arena, cdst.bvecs, cdst.first, cdst.iters.copy(), cdst.npages_used)
+    csrc.iters["bi_size"] = sizes.astype(np.uint32)
+    rets, faults = emu.decompress(simt, csrc, out, group=group, stage_cap=0, scratch_stride=16384)
+    assert faults == 0
+    assert np.array_equal(rets, [len(d) for d in datas])
+    for b, d in enumerate(datas):
+        assert np.array_equal(out.read_block(b), d), b
