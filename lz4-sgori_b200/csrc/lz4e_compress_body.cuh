@@ -96,6 +96,20 @@ LZ4E_DEV uint32_t lz4e_hash(uint32_t seq, uint32_t byte4, int tt)
 	return (seq * 2654435761U) >> (tt == LZ4E_TT_U16 ? 19 : 21);
 }
 
+/* the 4 bytes at p (little endian) and the byte after them, from two aligned
+ * words */
+LZ4E_DEV uint32_t lz4e_ld_seq5(const uint8_t *p, uint32_t &byte4)
+{
+	const uintptr_t ad = (uintptr_t)p;
+	const uint8_t *al = (const uint8_t *)(ad & ~(uintptr_t)3);
+	const uint32_t sh = (uint32_t)(ad & 3) * 8u;
+	const uint32_t w0 = lz4e_ld32a(al);
+	const uint32_t w1 = lz4e_ld32a(al + 4);
+
+	byte4 = (w1 >> sh) & 0xffu;
+	return lz4e_funnel_r(w0, w1, sh);
+}
+
 struct lz4e_out_stage {
 	uint8_t *base;	    /* staging area (shared memory) */
 	uint8_t *cur0;	    /* address holding output byte `win` */
@@ -235,9 +249,12 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 			 * zeroed table of positions; search starts at 1 */
 			uint32_t p0 = 1;
 			int kbase = 0;
+			bool have = false; /* (ip, mp) already known, see below */
+			uint32_t ip = 0, mp = 0;
 
 			src_end = 1;
 			for (;;) {
+				if (!have) {
 				/* ---- one speculative batch of 32 visits ---- */
 				const int k = kbase + (int)lane;
 				uint32_t pos, seq = 0, h = 0xffffffffu, m = 0;
@@ -307,28 +324,58 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 				    (peers & ((2u << f) - 1u) & ~((2u << lane) - 1u)) == 0)
 					tab[h] = (uint16_t)pos;
 
-				const uint32_t ip = lz4e_shfl(LZ4E_FULL, pos, f);
-				const uint32_t mp = lz4e_shfl(LZ4E_FULL, m, f);
+				ip = lz4e_shfl(LZ4E_FULL, pos, f);
+				mp = lz4e_shfl(LZ4E_FULL, m, f);
+				lz4e_syncwarp(LZ4E_FULL); /* table writes visible */
+				}
 
-				/* ---- catch up (:339-349) and match length
-				 * (lz4e_defs.h:587-636): one byte per lane each way ---- */
+				/*
+				 * ---- catch up (:339-349), match length (lz4e_defs.h:587-636)
+				 * and the NEXT "test next position" (:461-493), all at once ----
+				 * One byte per lane each way.  Lane j also assumes the match
+				 * is j bytes long, i.e. that the next anchor is q = ip + 4 + j,
+				 * and evaluates what the reference does there: table[H(q-2)] =
+				 * q-2, candidate = table[H(q)], compare 4 bytes.  The table is
+				 * not touched between the match decision and that point, so
+				 * reading it now is exact; once the length is known the lane
+				 * that guessed right hands over its result and the serial
+				 * chain from one match to the next is a single round of loads.
+				 */
 				uint32_t back = 0, ml;
+				uint32_t q_h = 0, q_h2 = 0, q_m = 0;
+				bool q_ok = false;
 				{
 					const uint32_t fip = ip + 4u, fm = mp + 4u;
 					const uint32_t limit = matchlimit - fip;
+					const uint32_t q = fip + lane;
 					uint32_t lim = ip - anchor;
-					bool beq = false, fne = true;
+					uint32_t bne = 1u;
+					bool fne = true;
 
 					if (mp < lim)
 						lim = mp;
-					if (lane < lim)
-						beq = d[ip - 1u - lane] == d[mp - 1u - lane];
 					if (lane < limit)
 						fne = d[fip + lane] != d[fm + lane];
-					const uint32_t bne = lz4e_ballot(LZ4E_FULL, !beq);
+					if (q <= mflimit) {
+						uint32_t b4q, b4p;
+						const uint32_t sq = lz4e_ld_seq5(d + q, b4q);
+						const uint32_t sp = lz4e_ld_seq5(d + q - 2u, b4p);
+
+						q_h = lz4e_hash(sq, b4q, tt);
+						q_h2 = lz4e_hash(sp, b4p, tt);
+						q_m = q_h2 == q_h ? q - 2u : (uint32_t)tab[q_h];
+						q_ok = q_m + 65535u >= q && lz4e_ld32u(d + q_m) == sq;
+					}
+					if (lim) { /* uniform: 0 after an immediate match */
+						bool beq = false;
+
+						if (lane < lim)
+							beq = d[ip - 1u - lane] == d[mp - 1u - lane];
+						bne = lz4e_ballot(LZ4E_FULL, !beq);
+						back = bne ? (uint32_t)lz4e_ffs(bne) - 1u : 32u;
+					}
 					const uint32_t fnz = lz4e_ballot(LZ4E_FULL, fne);
 
-					back = bne ? (uint32_t)lz4e_ffs(bne) - 1u : 32u;
 					while (bne == 0 && back < lim) { /* rare: > 32 back */
 						const uint32_t i = back + lane;
 						bool eq = false;
@@ -345,7 +392,9 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 					}
 					if (fnz) {
 						ml = (uint32_t)lz4e_ffs(fnz) - 1u;
+						have = true; /* lane ml holds the next test */
 					} else {
+						have = false;
 						/* >= 32 equal bytes: continue 4 bytes per lane */
 						ml = 32u;
 						for (;;) {
@@ -453,7 +502,25 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 					break;
 				}
 				p0 = anchor + 1u;
-				kbase = -2;
+				if (have) {
+					/* the lane that assumed length ml did the work of
+					 * :461-493 for this anchor; apply its table writes in
+					 * the reference's order */
+					const uint32_t okm = lz4e_ballot(LZ4E_FULL, q_ok);
+					const uint32_t nh = lz4e_shfl(LZ4E_FULL, q_h, (int)ml);
+					const uint32_t nh2 = lz4e_shfl(LZ4E_FULL, q_h2, (int)ml);
+
+					mp = lz4e_shfl(LZ4E_FULL, q_m, (int)ml);
+					if (lane == 0) {
+						tab[nh2] = (uint16_t)(anchor - 2u);
+						tab[nh] = (uint16_t)anchor;
+					}
+					ip = anchor;
+					have = (okm >> ml) & 1u; /* else: search from ip + 1 */
+					kbase = 0;
+				} else {
+					kbase = -2;
+				}
 				lz4e_syncwarp(LZ4E_FULL); /* table writes visible */
 			}
 		}
