@@ -147,69 +147,26 @@ LZ4E_DEV void lz4e_put_run(uint8_t *p, uint32_t count, uint32_t last,
 }
 
 /*
- * Compress block b.  sm points at this warp's shared memory
- * (lz4e_compress_smem_bytes()).  All 32 lanes call it together.
+ * The encoder proper for one gathered block: d[0..n) in shared memory, table
+ * `tab` (not yet cleared), output staging `out_area`.  TT is the hash-table
+ * address mode LZ4E_fillBvIterSize selected (lz4e_compress.c:184-211).
+ * Returns the reference's return value; src_end/dst_end receive the iterator
+ * end state.
  */
-LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
-				  uint8_t *sm, uint32_t lane)
+template <int TT>
+LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
+				      const struct lz4e_b200_dev_iter &di,
+				      const uint8_t *d, uint32_t n, uint8_t *sm,
+				      uint8_t *out_area, uint32_t lane,
+				      uint32_t &src_end, uint32_t &dst_end)
 {
-	const struct lz4e_b200_dev_iter si = a.src_iters[b];
-	const struct lz4e_b200_dev_iter di = a.dst_iters[b];
-	const uint32_t n = si.bi_size;
 	const uint32_t cap = di.bi_size;
 	uint16_t *tab = reinterpret_cast<uint16_t *>(sm);
-	uint8_t *in_area = sm + a.table_bytes;
-	uint8_t *out_area = in_area + a.in_cap + LZ4E_K_PAD;
-	const uint8_t *d; /* d[pos] = source byte at linear position pos */
-	int tt = LZ4E_TT_U16;
 	int32_t ret = 0;
-	uint32_t src_end = 0, dst_end = 0;
 
-	if (n > LZ4E_K_MAX_INPUT) /* lz4e_compress.c:245-248 */
-		goto done;
-	if (n > a.in_cap || n > 65536u) {
-		if (lane == 0)
-			lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
-		goto done;
-	}
-
-	/* ---- gather + address mode (lz4e_compress.c:184-211) ---- */
-	{
-		const struct lz4e_b200_dev_bvec *v =
-			a.src_bvecs + si.first + si.bi_idx;
-		uint32_t done_in = si.bi_bvec_done, rem = n, pos = 0, i = 0;
-		bool too_many = false;
-		uint8_t *dbase = in_area;
-
-		if (n)
-			dbase += (uint32_t)(v->addr + done_in) & 15u;
-		d = dbase;
-		while (rem) {
-			if (i >= BIO_MAX_VECS) {
-				too_many = true;
-				break;
-			}
-			const uint32_t len = v[i].len;
-			uint32_t take = len - done_in;
-			uint8_t *g = (uint8_t *)(uintptr_t)(v[i].addr + done_in);
-
-			LZ4E_ASSUME_GLOBAL(g);
-			if (i >= 16 || len > 4096u)
-				tt |= LZ4E_TT_U32;
-			if (len > (1u << 24))
-				tt |= LZ4E_TT_U64;
-			if (take > rem)
-				take = rem;
-			lz4e_copy<32>(dbase + pos, g, take, lane);
-			pos += take;
-			rem -= take;
-			done_in = 0;
-			i++;
-		}
-		if (too_many && n >= 13) /* :268-277 */
-			goto done;
-		lz4e_syncwarp(LZ4E_FULL); /* gathered bytes visible to all lanes */
-	}
+	LZ4E_ASSUME_SHARED(d);
+	LZ4E_ASSUME_SHARED(sm);
+	LZ4E_ASSUME_SHARED(out_area);
 
 	{
 		const bool limited = cap < n + n / 255u + 16u; /* :553 */
@@ -217,6 +174,7 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 		const uint32_t matchlimit = n - 5u;
 		/* the whole output fits the staging area: one flush at the end */
 		const bool whole = a.out_cap >= (cap < n + n / 255u + 16u ? cap : n + n / 255u + 16u);
+		const bool fast_ok = whole && !limited;
 		uint32_t anchor = 0, op = 0;
 		lz4e_out_stage st;
 
@@ -229,8 +187,8 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 
 		if (n >= 13) {
 			/* zero the table: (1 << hashLog) 16-bit entries */
-			const uint32_t tbytes = tt == LZ4E_TT_U16   ? 16384u
-						: tt == LZ4E_TT_U32 ? 8192u
+			const uint32_t tbytes = TT == LZ4E_TT_U16   ? 16384u
+						: TT == LZ4E_TT_U32 ? 8192u
 								    : 4096u;
 			const lz4e_u128 z = { 0, 0, 0, 0 };
 
@@ -238,7 +196,7 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 				/* launched for byU32-only batches, block wants byU16 */
 				if (lane == 0)
 					lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
-				goto done;
+				return 0;
 			}
 
 			for (uint32_t i = lane * 16u; i < tbytes; i += 512u)
@@ -281,7 +239,7 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 					const uint32_t w1 = lz4e_ld32a(al + 4);
 
 					seq = lz4e_funnel_r(w0, w1, sh);
-					h = lz4e_hash(seq, (w1 >> sh) & 0xffu, tt);
+					h = lz4e_hash(seq, (w1 >> sh) & 0xffu, TT);
 					m = tab[h];
 				}
 				const uint32_t peers = lz4e_match_any(LZ4E_FULL, h);
@@ -327,7 +285,80 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 				ip = lz4e_shfl(LZ4E_FULL, pos, f);
 				mp = lz4e_shfl(LZ4E_FULL, m, f);
 				lz4e_syncwarp(LZ4E_FULL); /* table writes visible */
+				have = true;
 				}
+
+				/*
+				 * ---- fast chain: a match that starts exactly at the anchor
+				 * (no literals, no catch-up) and is shorter than 36 bytes ----
+				 * This is what "test next position" (:467-493) produces over
+				 * and over on compressible data.  Lane j assumes the match is
+				 * j bytes past the minimum, i.e. that the next anchor is
+				 * q = ip + 4 + j, and evaluates the reference's next test
+				 * there (table[H(q-2)] = q-2; candidate = table[H(q)]; compare
+				 * 4 bytes) from three aligned words around q-2; the table is
+				 * not touched between the match decision and that test, so
+				 * reading it now is exact.  The lane that guessed right hands
+				 * its result over.
+				 */
+				bool ended = false;
+
+				while (fast_ok && have && ip == anchor) {
+					const uint32_t fip = ip + 4u, q = fip + lane;
+					const uintptr_t ad = (uintptr_t)(d + q - 2u);
+					const uint8_t *al = (const uint8_t *)(ad & ~(uintptr_t)3);
+					const uint32_t sh = (uint32_t)(ad & 3) * 8u;
+					const uint32_t w0 = lz4e_ld32a(al), w1 = lz4e_ld32a(al + 4),
+						       w2 = lz4e_ld32a(al + 8);
+					const uint32_t lo = lz4e_funnel_r(w0, w1, sh); /* bytes q-2.. */
+					const uint32_t hi = lz4e_funnel_r(w1, w2, sh); /* bytes q+2.. */
+					const uint32_t sq = lz4e_funnel_r(lo, hi, 16u); /* bytes q..   */
+					const uint32_t qh = lz4e_hash(sq, (hi >> 16) & 0xffu, TT);
+					const uint32_t qh2 = lz4e_hash(lo, hi & 0xffu, TT);
+					const uint32_t qm = qh2 == qh ? q - 2u : (uint32_t)tab[qh];
+					const bool fne = lane >= matchlimit - fip ||
+							 (sq & 0xffu) != d[mp + 4u + lane];
+					const bool qok = qm + 65535u >= q && lz4e_ld32u(d + qm) == sq;
+					const uint32_t fnz = lz4e_ballot(LZ4E_FULL, fne);
+
+					if (fnz == 0)
+						break; /* >= 32 more bytes: general path */
+					const uint32_t ml = (uint32_t)lz4e_ffs(fnz) - 1u;
+					const uint32_t na = fip + ml;
+					const uint32_t off = ip - mp;
+					uint8_t *o = st.cur0 + (op - st.win);
+
+					if (lane < 3u || (lane == 3u && ml >= 15u))
+						o[lane] = (uint8_t)(lane == 0   ? (ml < 15u ? ml : 15u)
+								    : lane == 1 ? off
+								    : lane == 2 ? off >> 8
+										: ml - 15u);
+					op += 3u + (ml >= 15u ? 1u : 0u);
+					anchor = na;
+					if (na > mflimit) { /* :456 */
+						src_end = na;
+						ended = true;
+						break;
+					}
+					const uint32_t okm = lz4e_ballot(LZ4E_FULL, qok);
+					const uint32_t nh = lz4e_shfl(LZ4E_FULL, qh, (int)ml);
+					const uint32_t nh2 = lz4e_shfl(LZ4E_FULL, qh2, (int)ml);
+
+					mp = lz4e_shfl(LZ4E_FULL, qm, (int)ml);
+					if (lane == 0) {
+						tab[nh2] = (uint16_t)(na - 2u);
+						tab[nh] = (uint16_t)na;
+					}
+					ip = na;
+					have = (okm >> ml) & 1u;
+					p0 = na + 1u; /* else: search from ip + 1 */
+					kbase = 0;
+					lz4e_syncwarp(LZ4E_FULL); /* table writes visible */
+				}
+				if (ended)
+					break;
+				if (!have)
+					continue;
 
 				/*
 				 * ---- catch up (:339-349), match length (lz4e_defs.h:587-636)
@@ -361,8 +392,8 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 						const uint32_t sq = lz4e_ld_seq5(d + q, b4q);
 						const uint32_t sp = lz4e_ld_seq5(d + q - 2u, b4p);
 
-						q_h = lz4e_hash(sq, b4q, tt);
-						q_h2 = lz4e_hash(sp, b4p, tt);
+						q_h = lz4e_hash(sq, b4q, TT);
+						q_h2 = lz4e_hash(sp, b4p, TT);
 						q_m = q_h2 == q_h ? q - 2u : (uint32_t)tab[q_h];
 						q_ok = q_m + 65535u >= q && lz4e_ld32u(d + q_m) == sq;
 					}
@@ -437,7 +468,7 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 					if (limited &&
 					    (op + 1u + lit + 8u + lit / 255u > cap ||
 					     op + 1u + lit_ext + lit + 2u + 6u + (mc >> 8) > cap))
-						goto done; /* ret stays 0 */
+						return 0;
 
 					bool stream = false;
 
@@ -531,7 +562,7 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 			const uint32_t ext = run >= 15u ? (run - 15u) / 255u + 1u : 0u;
 
 			if (limited && op + run + 1u + (run + 240u) / 255u > cap)
-				goto done;
+				return 0;
 			if (op - st.win + 1u + ext > st.cap)
 				lz4e_stage_flush(st, op, a.out_cap, lane);
 			uint8_t *o = st.cur0 + (op - st.win);
@@ -553,6 +584,87 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 			}
 			ret = (int32_t)op;
 		}
+	}
+
+	return ret;
+}
+
+/*
+ * Compress block b.  sm points at this warp's shared memory
+ * (lz4e_compress_smem_bytes()).  All 32 lanes call it together.
+ */
+LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
+				  uint8_t *sm, uint32_t lane)
+{
+	const struct lz4e_b200_dev_iter si = a.src_iters[b];
+	const struct lz4e_b200_dev_iter di = a.dst_iters[b];
+	const uint32_t n = si.bi_size;
+	uint8_t *in_area = sm + a.table_bytes;
+	uint8_t *out_area = in_area + a.in_cap + LZ4E_K_PAD;
+	const uint8_t *d; /* d[pos] = source byte at linear position pos */
+	int tt = LZ4E_TT_U16;
+	int32_t ret = 0;
+	uint32_t src_end = 0, dst_end = 0;
+
+	if (n > LZ4E_K_MAX_INPUT) /* lz4e_compress.c:245-248 */
+		goto done;
+	if (n > a.in_cap || n > 65536u) {
+		if (lane == 0)
+			lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
+		goto done;
+	}
+
+	/* ---- gather + address mode (lz4e_compress.c:184-211) ---- */
+	{
+		const struct lz4e_b200_dev_bvec *v =
+			a.src_bvecs + si.first + si.bi_idx;
+		uint32_t done_in = si.bi_bvec_done, rem = n, pos = 0, i = 0;
+		bool too_many = false;
+		uint8_t *dbase = in_area;
+
+		if (n)
+			dbase += (uint32_t)(v->addr + done_in) & 15u;
+		d = dbase;
+		while (rem) {
+			if (i >= BIO_MAX_VECS) {
+				too_many = true;
+				break;
+			}
+			const uint32_t len = v[i].len;
+			uint32_t take = len - done_in;
+			uint8_t *g = (uint8_t *)(uintptr_t)(v[i].addr + done_in);
+
+			LZ4E_ASSUME_GLOBAL(g);
+			if (i >= 16 || len > 4096u)
+				tt |= LZ4E_TT_U32;
+			if (len > (1u << 24))
+				tt |= LZ4E_TT_U64;
+			if (take > rem)
+				take = rem;
+			lz4e_copy<32>(dbase + pos, g, take, lane);
+			pos += take;
+			rem -= take;
+			done_in = 0;
+			i++;
+		}
+		if (too_many && n >= 13) /* :268-277 */
+			goto done;
+		lz4e_syncwarp(LZ4E_FULL); /* gathered bytes visible to all lanes */
+	}
+
+	switch (tt) {
+	case LZ4E_TT_U16:
+		ret = lz4e_compress_encode<LZ4E_TT_U16>(a, di, d, n, sm, out_area, lane,
+							src_end, dst_end);
+		break;
+	case LZ4E_TT_U32:
+		ret = lz4e_compress_encode<LZ4E_TT_U32>(a, di, d, n, sm, out_area, lane,
+							src_end, dst_end);
+		break;
+	default:
+		ret = lz4e_compress_encode<LZ4E_TT_U64>(a, di, d, n, sm, out_area, lane,
+							src_end, dst_end);
+		break;
 	}
 
 done:

@@ -21,6 +21,7 @@
 #define LZ4E_FULL 0xffffffffu
 /* address-space hint for pointers rebuilt from 64-bit descriptor fields */
 #define LZ4E_ASSUME_GLOBAL(p) __builtin_assume(__isGlobal(p))
+#define LZ4E_ASSUME_SHARED(p) __builtin_assume(__isShared(p))
 
 LZ4E_DEV uint32_t lz4e_ballot(uint32_t mask, int pred)
 {

@@ -19,6 +19,7 @@
 #define LZ4E_DEV static inline __attribute__((always_inline))
 #define LZ4E_FULL 0xffffffffu
 #define LZ4E_ASSUME_GLOBAL(p) ((void)(p))
+#define LZ4E_ASSUME_SHARED(p) ((void)(p))
 
 namespace simt
 {

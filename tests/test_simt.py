@@ -38,13 +38,14 @@ def _cases():
     return datas, specs
 
 
-def test_compress_body_matches_oracle(simt, ref_lib):
+@pytest.mark.parametrize("out_cap", [1024, 16384])  # streamed output / whole block staged
+def test_compress_body_matches_oracle(simt, ref_lib, out_cap):
     datas, specs = _cases()
     src = _host_layout(specs, datas)
     dspecs = [sg.segs_single(sg.compress_bound(len(d))) for d in datas]
     dst = _host_layout(dspecs)
     dst.arena.mem[:] = 0xEE
-    rets, ends, faults = emu.compress(simt, src, dst, in_cap=12288, out_cap=1024)
+    rets, ends, faults = emu.compress(simt, src, dst, in_cap=12288, out_cap=out_cap)
     ref_dst, (ref_rets, _, so, do) = common.oracle_compress(ref_lib, src, dspecs, want_iters=True)
     assert faults == 0
     assert np.array_equal(rets, ref_rets)

@@ -1,0 +1,56 @@
+#!/usr/bin/env python
+"""tools/class_bench.py — per content class timing (4 KiB blocks, one bvec):
+usage: class_bench.py [nblocks] [reps]"""
+import importlib
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+
+pkg = importlib.import_module("lz4-sgori_b200")
+
+
+def main():
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
+    reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+    ctx = pkg.Context(0)
+    d_src, d_dst, d_out = ctx.dev_alloc(n * 4096), ctx.dev_alloc(n * bench.DST_STRIDE), ctx.dev_alloc(n * 4096)
+    (sbv, sit), (dbv, dit), (obv, oit) = bench.cfg2_tables(pkg, d_src, d_dst, d_out, n)
+    t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
+    r1, r2 = ctx.dev_alloc(4 * n), ctx.dev_alloc(4 * n)
+    host = np.zeros((n, 4096), dtype=np.uint8)
+    for cls in range(4):
+        for b in range(n):
+            pkg.lib().lz4e_b200_synth_fill_host(host[b].ctypes.data, 4096, cls, 4 * b + cls)
+        ctx.check(pkg.lib().lz4e_b200_copy_h2d(ctx.h, None, d_src, host.ctypes.data, n * 4096), "h2d")
+        ctx.sync()
+        ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1)
+        ctx.sync()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1)
+        ctx.sync()
+        tc = (time.perf_counter() - t0) / reps
+        rets = ctx.download(r1, np.int32, n)
+        cit = dit.copy()
+        cit["bi_size"] = rets.astype(np.uint32)
+        d_cit = ctx.upload(cit)
+        ctx.decompress_dev(t[2], d_cit, t[4], t[5], n, int(rets.max()), 4096, r2, flags=pkg.DEV_DST_LINEAR)
+        ctx.sync()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            ctx.decompress_dev(t[2], d_cit, t[4], t[5], n, int(rets.max()), 4096, r2, flags=pkg.DEV_DST_LINEAR)
+        ctx.sync()
+        td = (time.perf_counter() - t0) / reps
+        assert (ctx.download(r2, np.int32, n) == 4096).all()
+        print("class %d: ratio %.2f  compress %.2f GB/s (%.1f us/block/warp-slot)  decompress %.2f GB/s" %
+              (cls, n * 4096 / rets.sum(), n * 4096 / tc / 1e9, tc * 1e6, n * 4096 / td / 1e9))
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()
