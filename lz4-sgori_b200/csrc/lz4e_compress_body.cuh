@@ -328,11 +328,13 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					const uint32_t off = ip - mp;
 					uint8_t *o = st.cur0 + (op - st.win);
 
-					if (lane < 3u || (lane == 3u && ml >= 15u))
-						o[lane] = (uint8_t)(lane == 0   ? (ml < 15u ? ml : 15u)
-								    : lane == 1 ? off
-								    : lane == 2 ? off >> 8
-										: ml - 15u);
+					/* token, offset (LE16) and, from 15 on, one length byte:
+					 * lane l stores byte l of one packed word */
+					const uint32_t word = (ml < 15u ? ml : 15u) | (off << 8) |
+							      ((ml - 15u) << 24);
+
+					if (lane < 3u + (ml >= 15u ? 1u : 0u))
+						o[lane] = (uint8_t)(word >> (8u * lane));
 					op += 3u + (ml >= 15u ? 1u : 0u);
 					anchor = na;
 					if (na > mflimit) { /* :456 */
