@@ -377,18 +377,21 @@ def run_e2e(torch, pkg, ctx, args):
     for b in range(nb):
         pkg.lib().lz4e_b200_synth_fill_host(mem[b].ctypes.data, BLOCK, b & 3, b)
     creqs, keep1 = pkg.make_reqs(src, dst)
+    # the decompress requests read the compressed blocks where compress left them; only the
+    # compressed sizes change from step to step
+    csrc = sg.Layout(dst_arena, dst.bvecs, dst.first, dst.iters.copy(), dst.npages_used)
+    dreqs, keep2 = pkg.make_reqs(csrc, out)
+    d_src_iters = keep2[0]
 
     def once():
         creqs["ret"] = 0
         rc = ctx.compress_batch(creqs, flags=pkg.F_KEEP_ITERS)
         assert rc == 0, ctx.err()
-        sizes = creqs["ret"].copy()
-        csrc = sg.Layout(dst_arena, dst.bvecs, dst.first, dst.iters.copy(), dst.npages_used)
-        csrc.iters["bi_size"] = sizes.astype(np.uint32)
-        dreqs, keep2 = pkg.make_reqs(csrc, out)
+        sizes = creqs["ret"]
+        d_src_iters["bi_size"] = sizes
         rc = ctx.decompress_batch(dreqs, flags=0)
         assert rc == 0, ctx.err()
-        return sizes, dreqs["ret"].copy()
+        return sizes.copy(), dreqs["ret"].copy()
 
     for _ in range(2):
         sizes, r2 = once()
@@ -400,7 +403,6 @@ def run_e2e(torch, pkg, ctx, args):
         once()
     dt = (time.perf_counter() - t0) / reps
     tables = nb * (16 + 16 + 16 + 16)
-    h2d = nb * BLOCK + tables + int(sizes.sum() // 1) + tables     # pages + tables, both passes (approx. ranges)
     h2d = nb * BLOCK + tables + nb * DST_STRIDE + tables
     d2h = nb * DST_STRIDE + nb * 12 + nb * BLOCK + nb * 12
     for a in (src_arena, dst_arena, out_arena):

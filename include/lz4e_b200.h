@@ -180,6 +180,16 @@ int lz4e_b200_copy_h2d(lz4e_b200_ctx *ctx, void *stream, void *dst_dev,
 int lz4e_b200_copy_d2h(lz4e_b200_ctx *ctx, void *stream, void *dst_host,
 		       const void *src_dev, size_t bytes);
 
+/* streams and events for callers that pipeline *_dev calls with copies (the
+ * host-level batches do): opaque cudaStream_t / cudaEvent_t handles */
+void *lz4e_b200_stream_create(lz4e_b200_ctx *ctx);
+void lz4e_b200_stream_destroy(lz4e_b200_ctx *ctx, void *stream);
+void *lz4e_b200_event_create(lz4e_b200_ctx *ctx);
+void lz4e_b200_event_destroy(lz4e_b200_ctx *ctx, void *event);
+int lz4e_b200_event_record(lz4e_b200_ctx *ctx, void *event, void *stream);
+/* work enqueued on `stream` after this call waits for `event` */
+int lz4e_b200_stream_wait_event(lz4e_b200_ctx *ctx, void *stream, void *event);
+
 /* ---- layer 2: page arenas ------------------------------------------------ */
 int lz4e_b200_arena_create(lz4e_b200_ctx *ctx, size_t npages,
 			   lz4e_b200_arena **out);
@@ -191,6 +201,9 @@ int lz4e_b200_arena_upload(lz4e_b200_arena *arena, size_t first_page,
 			   size_t npages);
 int lz4e_b200_arena_download(lz4e_b200_arena *arena, size_t first_page,
 			     size_t npages);
+/* the context's arenas (at most `max` of them); returns how many were stored */
+size_t lz4e_b200_arena_snapshot(lz4e_b200_ctx *ctx, lz4e_b200_arena **out,
+				size_t max);
 /* device address mirroring host address `p` if it lies in an arena of ctx,
  * else 0; *arena_out (optional) receives the arena */
 uint64_t lz4e_b200_arena_translate(lz4e_b200_ctx *ctx, const void *p,
