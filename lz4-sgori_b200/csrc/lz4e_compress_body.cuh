@@ -96,18 +96,29 @@ LZ4E_DEV uint32_t lz4e_hash(uint32_t seq, uint32_t byte4, int tt)
 	return (seq * 2654435761U) >> (tt == LZ4E_TT_U16 ? 19 : 21);
 }
 
-/* the 4 bytes at p (little endian) and the byte after them, from two aligned
- * words */
-LZ4E_DEV uint32_t lz4e_ld_seq5(const uint8_t *p, uint32_t &byte4)
+/*
+ * Word access to the gathered block.  `da` is the 4-byte aligned shared-memory
+ * address just below the block's byte 0 and `t` = position + (d - da), so the
+ * aligned word holding a byte is da + (t & ~3) with 32-bit arithmetic only:
+ * the address keeps its shared address space (LDS, no generic 64-bit math).
+ * The funnel shift takes its count modulo 32, so t << 3 is the bit offset.
+ */
+LZ4E_DEV uint32_t lz4e_sld32u(const uint8_t *da, uint32_t t)
 {
-	const uintptr_t ad = (uintptr_t)p;
-	const uint8_t *al = (const uint8_t *)(ad & ~(uintptr_t)3);
-	const uint32_t sh = (uint32_t)(ad & 3) * 8u;
+	const uint8_t *al = da + (t & ~3u);
+
+	return lz4e_funnel_r(lz4e_ld32a(al), lz4e_ld32a(al + 4), t << 3);
+}
+
+/* the 4 bytes at t (little endian) and the byte after them */
+LZ4E_DEV uint32_t lz4e_sld_seq5(const uint8_t *da, uint32_t t, uint32_t &byte4)
+{
+	const uint8_t *al = da + (t & ~3u);
 	const uint32_t w0 = lz4e_ld32a(al);
 	const uint32_t w1 = lz4e_ld32a(al + 4);
 
-	byte4 = (w1 >> sh) & 0xffu;
-	return lz4e_funnel_r(w0, w1, sh);
+	byte4 = (w1 >> ((t & 3u) * 8u)) & 0xffu;
+	return lz4e_funnel_r(w0, w1, t << 3);
 }
 
 struct lz4e_out_stage {
@@ -167,6 +178,11 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 	LZ4E_ASSUME_SHARED(d);
 	LZ4E_ASSUME_SHARED(sm);
 	LZ4E_ASSUME_SHARED(out_area);
+	/* see lz4e_sld32u(): aligned base and the block's offset from it */
+	const uint32_t dm = (uint32_t)(uintptr_t)d & 3u;
+	const uint8_t *da = d - dm;
+
+	LZ4E_ASSUME_SHARED(da);
 
 	{
 		const bool limited = cap < n + n / 255u + 16u; /* :553 */
@@ -231,15 +247,10 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					valid = pos + step <= mflimit;
 				}
 				if (valid) {
-					const uintptr_t ad = (uintptr_t)(d + pos);
-					const uint8_t *al =
-						(const uint8_t *)(ad & ~(uintptr_t)3);
-					const uint32_t sh = (uint32_t)(ad & 3) * 8u;
-					const uint32_t w0 = lz4e_ld32a(al);
-					const uint32_t w1 = lz4e_ld32a(al + 4);
+					uint32_t b4;
 
-					seq = lz4e_funnel_r(w0, w1, sh);
-					h = lz4e_hash(seq, (w1 >> sh) & 0xffu, TT);
+					seq = lz4e_sld_seq5(da, pos + dm, b4);
+					h = lz4e_hash(seq, b4, TT);
 					m = tab[h];
 				}
 				const uint32_t peers = lz4e_match_any(LZ4E_FULL, h);
@@ -251,7 +262,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				if (lower)
 					m = mj;
 				if (valid && k != -2 && m + 65535u >= pos)
-					ok = lz4e_ld32u(d + m) == seq;
+					ok = lz4e_sld32u(da, m + dm) == seq;
 
 				const uint32_t okmask = lz4e_ballot(LZ4E_FULL, ok);
 
@@ -303,11 +314,12 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				 */
 				bool ended = false;
 
-				while (fast_ok && have && ip == anchor) {
+				if (fast_ok && have && ip == anchor) {
+				for (;;) {
 					const uint32_t fip = ip + 4u, q = fip + lane;
-					const uintptr_t ad = (uintptr_t)(d + q - 2u);
-					const uint8_t *al = (const uint8_t *)(ad & ~(uintptr_t)3);
-					const uint32_t sh = (uint32_t)(ad & 3) * 8u;
+					const uint32_t tq = q - 2u + dm;
+					const uint8_t *al = da + (tq & ~3u);
+					const uint32_t sh = tq << 3;
 					const uint32_t w0 = lz4e_ld32a(al), w1 = lz4e_ld32a(al + 4),
 						       w2 = lz4e_ld32a(al + 8);
 					const uint32_t lo = lz4e_funnel_r(w0, w1, sh); /* bytes q-2.. */
@@ -318,7 +330,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					const uint32_t qm = qh2 == qh ? q - 2u : (uint32_t)tab[qh];
 					const bool fne = lane >= matchlimit - fip ||
 							 (sq & 0xffu) != d[mp + 4u + lane];
-					const bool qok = qm + 65535u >= q && lz4e_ld32u(d + qm) == sq;
+					const bool qok = qm + 65535u >= q && lz4e_sld32u(da, qm + dm) == sq;
 					const uint32_t fnz = lz4e_ballot(LZ4E_FULL, fne);
 
 					if (fnz == 0)
@@ -327,6 +339,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					const uint32_t na = fip + ml;
 					const uint32_t off = ip - mp;
 					uint8_t *o = st.cur0 + (op - st.win);
+					const bool last = na > mflimit; /* :456 */
 
 					/* token, offset (LE16) and, from 15 on, one length byte:
 					 * lane l stores byte l of one packed word */
@@ -336,29 +349,29 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					if (lane < 3u + (ml >= 15u ? 1u : 0u))
 						o[lane] = (uint8_t)(word >> (8u * lane));
 					op += 3u + (ml >= 15u ? 1u : 0u);
-					anchor = na;
-					if (na > mflimit) { /* :456 */
-						src_end = na;
-						ended = true;
-						break;
-					}
 					const uint32_t okm = lz4e_ballot(LZ4E_FULL, qok);
-					const uint32_t nh = lz4e_shfl(LZ4E_FULL, qh, (int)ml);
-					const uint32_t nh2 = lz4e_shfl(LZ4E_FULL, qh2, (int)ml);
 
 					mp = lz4e_shfl(LZ4E_FULL, qm, (int)ml);
-					if (lane == 0) {
-						tab[nh2] = (uint16_t)(na - 2u);
-						tab[nh] = (uint16_t)na;
+					/* the lane that guessed the length holds the hashes of
+					 * :461-464 and :467-470 for the new anchor q == na */
+					if (lane == ml && !last) {
+						tab[qh2] = (uint16_t)(q - 2u);
+						tab[qh] = (uint16_t)q;
 					}
-					ip = na;
-					have = (okm >> ml) & 1u;
-					p0 = na + 1u; /* else: search from ip + 1 */
+					anchor = ip = na;
+					p0 = na + 1u; /* if no match follows: search from ip + 1 */
 					kbase = 0;
+					ended = last;
+					have = !last && ((okm >> ml) & 1u);
 					lz4e_syncwarp(LZ4E_FULL); /* table writes visible */
+					if (!have)
+						break;
 				}
-				if (ended)
+				}
+				if (ended) {
+					src_end = anchor;
 					break;
+				}
 				if (!have)
 					continue;
 
@@ -391,13 +404,13 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 						fne = d[fip + lane] != d[fm + lane];
 					if (q <= mflimit) {
 						uint32_t b4q, b4p;
-						const uint32_t sq = lz4e_ld_seq5(d + q, b4q);
-						const uint32_t sp = lz4e_ld_seq5(d + q - 2u, b4p);
+						const uint32_t sq = lz4e_sld_seq5(da, q + dm, b4q);
+						const uint32_t sp = lz4e_sld_seq5(da, q - 2u + dm, b4p);
 
 						q_h = lz4e_hash(sq, b4q, TT);
 						q_h2 = lz4e_hash(sp, b4p, TT);
 						q_m = q_h2 == q_h ? q - 2u : (uint32_t)tab[q_h];
-						q_ok = q_m + 65535u >= q && lz4e_ld32u(d + q_m) == sq;
+						q_ok = q_m + 65535u >= q && lz4e_sld32u(da, q_m + dm) == sq;
 					}
 					if (lim) { /* uniform: 0 after an immediate match */
 						bool beq = false;
@@ -435,8 +448,8 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 							uint32_t x = 1;
 
 							if (o < limit)
-								x = lz4e_ld32u(d + fip + o) ^
-								    lz4e_ld32u(d + fm + o);
+								x = lz4e_sld32u(da, fip + o + dm) ^
+								    lz4e_sld32u(da, fm + o + dm);
 							const uint32_t nz =
 								lz4e_ballot(LZ4E_FULL, x != 0);
 							if (nz) {
@@ -540,13 +553,11 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					 * :461-493 for this anchor; apply its table writes in
 					 * the reference's order */
 					const uint32_t okm = lz4e_ballot(LZ4E_FULL, q_ok);
-					const uint32_t nh = lz4e_shfl(LZ4E_FULL, q_h, (int)ml);
-					const uint32_t nh2 = lz4e_shfl(LZ4E_FULL, q_h2, (int)ml);
 
 					mp = lz4e_shfl(LZ4E_FULL, q_m, (int)ml);
-					if (lane == 0) {
-						tab[nh2] = (uint16_t)(anchor - 2u);
-						tab[nh] = (uint16_t)anchor;
+					if (lane == ml) {
+						tab[q_h2] = (uint16_t)(anchor - 2u);
+						tab[q_h] = (uint16_t)anchor;
 					}
 					ip = anchor;
 					have = (okm >> ml) & 1u; /* else: search from ip + 1 */
