@@ -176,7 +176,7 @@ def run_ours(args):
     d_rets, d_rets2 = ctx.dev_alloc(4 * nb), ctx.dev_alloc(4 * nb)
     ctx.synth_fill_dev(t[0], t[1], nb, first_index=int(first), stream=sp)
     ctx.sync(sp)
-    ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, stream=sp)
+    ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, flags=pkg.DEV_DST_LINEAR, stream=sp)
     ctx.sync(sp)
     rets = ctx.download(d_rets, np.int32, nb)
     assert (rets > 0).all()
@@ -188,13 +188,14 @@ def run_ours(args):
 
     def step(evs=None):
         if evs is not None:
-            evs.append(event_ms(torch, lambda: ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK,
-                                                                d_rets, stream=sp), stream))
+            evs.append(event_ms(torch, lambda: ctx.compress_dev(
+                t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, flags=pkg.DEV_DST_LINEAR, stream=sp),
+                stream))
             evs.append(event_ms(torch, lambda: ctx.decompress_dev(
                 t[2], d_cit, t[4], t[5], nb, max_c, BLOCK, d_rets2, flags=pkg.DEV_DST_LINEAR,
                 stream=sp), stream))
         else:
-            ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, stream=sp)
+            ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, flags=pkg.DEV_DST_LINEAR, stream=sp)
             ctx.decompress_dev(t[2], d_cit, t[4], t[5], nb, max_c, BLOCK, d_rets2,
                                flags=pkg.DEV_DST_LINEAR, stream=sp)
 

@@ -98,8 +98,10 @@ int lz4e_b200_sync(lz4e_b200_ctx *ctx, void *stream);
 #define LZ4E_B200_DEV_NO_BYU16 1u   /* compress: no block selects the byU16 table
 				     * (every block has a bv_len > 4096 or more
 				     * than 16 bvecs): halves the table footprint */
-#define LZ4E_B200_DEV_DST_LINEAR 2u /* decompress: every destination is one
-				     * contiguous segment: no scratch needed */
+#define LZ4E_B200_DEV_DST_LINEAR 2u /* every destination is one contiguous
+				     * segment holding the whole capacity:
+				     * decompress needs no scratch, compress
+				     * writes in place without staging */
 
 /*
  * LZ4E_compress_default for `nblocks` independent blocks.

@@ -482,8 +482,13 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 		a.out_cap = bound <= 4352u ? ((bound + 15u) & ~15u) + 16u : 2048u;
 		if (a.out_cap < 1024u)
 			a.out_cap = 1024u;
+		/* linear destinations are written in place: no staging, more
+		 * resident warps (4 KiB blocks: 9 -> 11 per SM) */
+		if (flags & LZ4E_B200_DEV_DST_LINEAR)
+			a.out_cap = 64u;
 	}
-	if (lz4e_launch_compress(&a, ctx->sm_count, s, nullptr)) {
+	if (lz4e_launch_compress(&a, (flags & LZ4E_B200_DEV_DST_LINEAR) ? 1 : 0, ctx->sm_count, s,
+				 nullptr)) {
 		set_err(ctx, "compress launch failed: %s",
 			cudaGetErrorString(cudaGetLastError()));
 		return LZ4E_B200_EIO;

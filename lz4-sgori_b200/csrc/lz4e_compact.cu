@@ -161,7 +161,8 @@ extern "C" int lz4e_b200_compress_compact_dev(
 	lz4e_slots_kernel<<<(nblocks + 255) / 256, 256, 0, s>>>(src_iters, scr, stride, sbv,
 								sit, nblocks);
 	int rc = lz4e_b200_compress_dev(ctx, (void *)s, src_bvecs, src_iters, sbv, sit, nblocks,
-					max_in_bytes, flags, rets, nullptr);
+					max_in_bytes, flags | LZ4E_B200_DEV_DST_LINEAR, rets,
+					nullptr);
 	if (rc)
 		return rc;
 	lz4e_scan_kernel<0><<<1, 1024, 0, s>>>(rets, nblocks, offsets);

@@ -164,7 +164,7 @@ LZ4E_DEV void lz4e_put_run(uint8_t *p, uint32_t count, uint32_t last,
  * Returns the reference's return value; src_end/dst_end receive the iterator
  * end state.
  */
-template <int TT>
+template <int TT, bool DIRECT>
 LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				      const struct lz4e_b200_dev_iter &di,
 				      const uint8_t *d, uint32_t n, uint8_t *sm,
@@ -177,7 +177,8 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 
 	LZ4E_ASSUME_SHARED(d);
 	LZ4E_ASSUME_SHARED(sm);
-	LZ4E_ASSUME_SHARED(out_area);
+	if (!DIRECT)
+		LZ4E_ASSUME_SHARED(out_area);
 	/* see lz4e_sld32u(): aligned base and the block's offset from it */
 	const uint32_t dm = (uint32_t)(uintptr_t)d & 3u;
 	const uint8_t *da = d - dm;
@@ -189,17 +190,25 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 		const uint32_t mflimit = n - 12u;
 		const uint32_t matchlimit = n - 5u;
 		/* the whole output fits the staging area: one flush at the end */
-		const bool whole = a.out_cap >= (cap < n + n / 255u + 16u ? cap : n + n / 255u + 16u);
+		const bool whole = DIRECT || a.out_cap >= (cap < n + n / 255u + 16u ? cap : n + n / 255u + 16u);
 		const bool fast_ok = whole && !limited;
 		uint32_t anchor = 0, op = 0;
 		lz4e_out_stage st;
 
 		st.base = out_area;
 		st.dst = lz4e_cursor_init(a.dst_bvecs, di);
-		if (cap)
+		if (DIRECT) {
+			/* the destination is one contiguous segment (checked by
+			 * the caller): sequences are stored where they belong,
+			 * no staging, no flush */
+			st.cur0 = cap ? lz4e_cursor_addr(st.dst) : out_area;
+			st.win = 0;
+			st.cap = 0xffffffffu;
+		} else if (cap) {
 			lz4e_stage_rebase(st, 0, a.out_cap);
-		else
+		} else {
 			st.cur0 = out_area, st.win = 0, st.cap = a.out_cap;
+		}
 
 		if (n >= 13) {
 			/* zero the table: (1 << hashLog) 16-bit entries */
@@ -576,7 +585,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 
 			if (limited && op + run + 1u + (run + 240u) / 255u > cap)
 				return 0;
-			if (op - st.win + 1u + ext > st.cap)
+			if (!DIRECT && op - st.win + 1u + ext > st.cap)
 				lz4e_stage_flush(st, op, a.out_cap, lane);
 			uint8_t *o = st.cur0 + (op - st.win);
 
@@ -585,7 +594,10 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 			lz4e_put_run(o + 1, ext, (run - 15u) % 255u, lane);
 			op += 1u + ext;
 			dst_end = op;
-			if (op - st.win + run > st.cap) {
+			if (DIRECT) {
+				lz4e_copy<32>(o + 1u + ext, d + anchor, run, lane);
+				op += run;
+			} else if (op - st.win + run > st.cap) {
 				lz4e_stage_flush(st, op, a.out_cap, lane);
 				lz4e_scatter<32>(st.dst, d + anchor, run, lane);
 				op += run;
@@ -606,6 +618,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
  * Compress block b.  sm points at this warp's shared memory
  * (lz4e_compress_smem_bytes()).  All 32 lanes call it together.
  */
+template <bool DIRECT>
 LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 				  uint8_t *sm, uint32_t lane)
 {
@@ -625,6 +638,17 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 		if (lane == 0)
 			lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
 		goto done;
+	}
+	if (DIRECT && di.bi_size) {
+		/* promise of LZ4E_B200_DEV_DST_LINEAR: one segment holds the whole
+		 * capacity */
+		const struct lz4e_b200_dev_bvec *dv = a.dst_bvecs + di.first + di.bi_idx;
+
+		if (dv->len < di.bi_bvec_done || dv->len - di.bi_bvec_done < di.bi_size) {
+			if (lane == 0)
+				lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
+			goto done;
+		}
 	}
 
 	/* ---- gather + address mode (lz4e_compress.c:184-211) ---- */
@@ -667,15 +691,15 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 
 	switch (tt) {
 	case LZ4E_TT_U16:
-		ret = lz4e_compress_encode<LZ4E_TT_U16>(a, di, d, n, sm, out_area, lane,
+		ret = lz4e_compress_encode<LZ4E_TT_U16, DIRECT>(a, di, d, n, sm, out_area, lane,
 							src_end, dst_end);
 		break;
 	case LZ4E_TT_U32:
-		ret = lz4e_compress_encode<LZ4E_TT_U32>(a, di, d, n, sm, out_area, lane,
+		ret = lz4e_compress_encode<LZ4E_TT_U32, DIRECT>(a, di, d, n, sm, out_area, lane,
 							src_end, dst_end);
 		break;
 	default:
-		ret = lz4e_compress_encode<LZ4E_TT_U64>(a, di, d, n, sm, out_area, lane,
+		ret = lz4e_compress_encode<LZ4E_TT_U64, DIRECT>(a, di, d, n, sm, out_area, lane,
 							src_end, dst_end);
 		break;
 	}
@@ -693,6 +717,7 @@ done:
 }
 
 /* persistent loop: warps pull block indices from a global counter */
+template <bool DIRECT>
 LZ4E_DEV void lz4e_compress_warp(const lz4e_compress_args &a, uint8_t *sm,
 				 uint32_t lane)
 {
@@ -704,7 +729,7 @@ LZ4E_DEV void lz4e_compress_warp(const lz4e_compress_args &a, uint8_t *sm,
 		b = lz4e_shfl(LZ4E_FULL, b, 0);
 		if (b >= a.nblocks)
 			break;
-		lz4e_compress_block(a, b, sm, lane);
+		lz4e_compress_block<DIRECT>(a, b, sm, lane);
 	}
 }
 

@@ -13,10 +13,11 @@
 extern __shared__ __align__(16) uint8_t lz4e_smem[];
 
 /* ---- K2: compression, one warp (= one CTA) per block in flight ----------- */
+template <bool DIRECT>
 __global__ void __launch_bounds__(32)
 lz4e_compress_kernel(const lz4e_compress_args a)
 {
-	lz4e_compress_warp(a, lz4e_smem, threadIdx.x);
+	lz4e_compress_warp<DIRECT>(a, lz4e_smem, threadIdx.x);
 }
 
 /* ---- K4: decompression, LZ4E_D_WARPS warps per CTA, 32/GS blocks per warp */
@@ -74,16 +75,17 @@ static int lz4e_set_smem(const void *fn, size_t bytes)
 		       : -1;
 }
 
-int lz4e_launch_compress(const lz4e_compress_args *a, int sm_count,
+int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int sm_count,
 			 cudaStream_t stream, int *grid_out)
 {
 	const size_t smem = lz4e_compress_smem_bytes(a->table_bytes, a->in_cap, a->out_cap);
 	int per_sm = 0;
+	auto fn = direct ? lz4e_compress_kernel<true> : lz4e_compress_kernel<false>;
 
-	if (lz4e_set_smem((const void *)lz4e_compress_kernel, smem))
+	if (lz4e_set_smem((const void *)fn, smem))
 		return -1;
-	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-		    &per_sm, lz4e_compress_kernel, 32, smem) != cudaSuccess ||
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 32, smem) !=
+		    cudaSuccess ||
 	    per_sm < 1)
 		return -1;
 	long long grid = (long long)per_sm * sm_count;
@@ -92,7 +94,7 @@ int lz4e_launch_compress(const lz4e_compress_args *a, int sm_count,
 		grid = a->nblocks;
 	if (grid < 1)
 		grid = 1;
-	lz4e_compress_kernel<<<(unsigned)grid, 32, smem, stream>>>(*a);
+	fn<<<(unsigned)grid, 32, smem, stream>>>(*a);
 	if (grid_out)
 		*grid_out = (int)grid;
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;

@@ -12,7 +12,7 @@
 struct lz4e_compress_args;
 struct lz4e_decompress_args;
 
-int lz4e_launch_compress(const lz4e_compress_args *a, int sm_count,
+int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int sm_count,
 			 cudaStream_t stream, int *grid_out);
 int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_count);
 int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,

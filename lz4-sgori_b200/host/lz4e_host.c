@@ -537,7 +537,9 @@ static int lane_submit(lz4e_b200_ctx *ctx, struct arena_set *as, struct lane *ln
 			(struct lz4e_b200_dev_iter *)(ln->dev + o_sit),
 			(struct lz4e_b200_dev_bvec *)(ln->dev + o_dbv),
 			(struct lz4e_b200_dev_iter *)(ln->dev + o_dit), (uint32_t)n,
-			ln->src.max_size, ln->src.any_u16 ? 0 : LZ4E_B200_DEV_NO_BYU16,
+			ln->src.max_size,
+			(ln->src.any_u16 ? 0 : LZ4E_B200_DEV_NO_BYU16) |
+				(ln->dst.all_linear ? LZ4E_B200_DEV_DST_LINEAR : 0),
 			(int32_t *)(ln->dev + ln->o_ret),
 			(struct lz4e_b200_dev_end *)(ln->dev + ln->o_end));
 	}

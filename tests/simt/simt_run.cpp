@@ -229,7 +229,12 @@ int simt_compress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 	a.out_cap = out_cap;
 	uint8_t *sm = (uint8_t *)smraw;
 
-	simt::run_warp([&](uint32_t lane) { lz4e_compress_warp(a, sm, lane); }, seed);
+	/* out_cap 64 = what lz4e_b200_compress_dev passes for linear destinations:
+	 * output written in place, no staging */
+	if (out_cap == 64)
+		simt::run_warp([&](uint32_t lane) { lz4e_compress_warp<true>(a, sm, lane); }, seed);
+	else
+		simt::run_warp([&](uint32_t lane) { lz4e_compress_warp<false>(a, sm, lane); }, seed);
 	free(smraw);
 	return 0;
 }

@@ -38,6 +38,8 @@ def test_config2_4k_mixed(ctx, ref_lib):
     datas = [common.synth(4096, b & 3, b) for b in range(n)]
     src, dst, rets = _check_compress(ctx, ref_lib, datas, [sg.segs_single(4096)] * n)
     assert rets[1] == 4114  # incompressible expands
+    # linear destinations written in place (no staging) give the same bytes
+    _check_compress(ctx, ref_lib, datas, [sg.segs_single(4096)] * n, flags=pkg.DEV_DST_LINEAR)
     # config 4: decompress what was produced, from the (multi-page) destination bvecs
     out = common.build_layout(_arena(ctx), [sg.segs_single(4096)] * n)
     r2 = common.gpu_decompress(ctx, dst, rets, out)
@@ -114,8 +116,10 @@ def test_limited_output(ctx, ref_lib):
             dspecs.append(dict(sg.segs_single(max(cap, 1)), size=cap))
     # a failed limitedOutput call leaves a partial (unspecified) prefix behind in both
     # implementations, so only successful blocks are compared byte for byte
-    _, _, rets = _check_compress(ctx, ref_lib, datas, specs, dspecs, check_untouched=False)
-    assert (rets[0::5] == sizes).all() and (rets[1::5] == 0).all()
+    for flags in (0, pkg.DEV_DST_LINEAR):
+        _, _, rets = _check_compress(ctx, ref_lib, datas, specs, dspecs, flags=flags,
+                                     check_untouched=False)
+        assert (rets[0::5] == sizes).all() and (rets[1::5] == 0).all()
 
 
 def test_too_many_bvecs(ctx, ref_lib):

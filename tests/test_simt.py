@@ -38,7 +38,8 @@ def _cases():
     return datas, specs
 
 
-@pytest.mark.parametrize("out_cap", [1024, 16384])  # streamed output / whole block staged
+# streamed output / whole block staged / written in place (linear destination)
+@pytest.mark.parametrize("out_cap", [1024, 16384, 64])
 def test_compress_body_matches_oracle(simt, ref_lib, out_cap):
     datas, specs = _cases()
     src = _host_layout(specs, datas)
@@ -56,7 +57,8 @@ def test_compress_body_matches_oracle(simt, ref_lib, out_cap):
             assert int(ends[b]["dst_pos"]) == int(dspecs[b]["size"]) - int(do[b]["bi_size"]), b
 
 
-def test_compress_body_limited_output(simt, ref_lib):
+@pytest.mark.parametrize("out_cap", [1024, 64])
+def test_compress_body_limited_output(simt, ref_lib, out_cap):
     datas = [common.synth(4096, c, 77 + c) for c in range(4)] * 3
     specs = [sg.segs_single(4096)] * len(datas)
     src = _host_layout(specs, datas)
@@ -66,7 +68,7 @@ def test_compress_body_limited_output(simt, ref_lib):
     caps = [int(s) + d for s, d in zip(sizes, [0, -1, -7, 5] * 3)]  # exact fit, too small, ...
     dspecs = [sg.segs_single(max(c, 1)) for c in caps]
     dst = _host_layout(dspecs)
-    rets, _, faults = emu.compress(simt, src, dst, in_cap=4096, out_cap=1024)
+    rets, _, faults = emu.compress(simt, src, dst, in_cap=4096, out_cap=out_cap)
     ref_dst, (ref_rets, _) = common.oracle_compress(ref_lib, src, dspecs)
     assert faults == 0
     assert np.array_equal(rets, ref_rets)

@@ -28,11 +28,11 @@ def main():
             pkg.lib().lz4e_b200_synth_fill_host(host[b].ctypes.data, 4096, cls, 4 * b + cls)
         ctx.check(pkg.lib().lz4e_b200_copy_h2d(ctx.h, None, d_src, host.ctypes.data, n * 4096), "h2d")
         ctx.sync()
-        ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1)
+        ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1, flags=pkg.DEV_DST_LINEAR)
         ctx.sync()
         t0 = time.perf_counter()
         for _ in range(reps):
-            ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1)
+            ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1, flags=pkg.DEV_DST_LINEAR)
         ctx.sync()
         tc = (time.perf_counter() - t0) / reps
         rets = ctx.download(r1, np.int32, n)

@@ -26,11 +26,11 @@ def main():
     t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
     r1, r2 = ctx.dev_alloc(4 * n4), ctx.dev_alloc(4 * n4)
     ctx.synth_fill_dev(t[0], t[1], n4)
-    ctx.compress_dev(t[0], t[1], t[2], t[3], n4, 4096, r1)
+    ctx.compress_dev(t[0], t[1], t[2], t[3], n4, 4096, r1, flags=pkg.DEV_DST_LINEAR)
     ctx.sync()
     t0 = time.perf_counter()
     for _ in range(reps):
-        ctx.compress_dev(t[0], t[1], t[2], t[3], n4, 4096, r1)
+        ctx.compress_dev(t[0], t[1], t[2], t[3], n4, 4096, r1, flags=pkg.DEV_DST_LINEAR)
     ctx.sync()
     tc = (time.perf_counter() - t0) / reps
     rets = ctx.download(r1, np.int32, n4)
