@@ -1,0 +1,602 @@
+/*
+ * lz4e_chunk.c — the lz4e_bdev chunk layer and request path in userspace, on
+ * the GPU LZ4E library.  Interface and behaviour follow the reference's
+ * lz4e_bdev/lz4e_chunk.c:19-159 and lz4e_bdev/lz4e_req.c:53-213 (see
+ * include/lz4e_chunk.h); the implementation is batch-first.
+ */
+#include <errno.h>
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/lz4e.h"
+#include "../../include/lz4e_chunk.h"
+
+/* ---- buffer pool: pinned pages with a device mirror ------------------------- */
+
+#define POOL_CLASSES 513 /* free lists for runs of 1..512 pages */
+
+struct run_hdr {
+	struct run_hdr *next;
+};
+
+static pthread_mutex_t p_mu = PTHREAD_MUTEX_INITIALIZER;
+static struct {
+	lz4e_b200_ctx *ctx;
+	lz4e_b200_arena *arena;
+	uint8_t *base;
+	size_t npages, bump;
+	struct run_hdr *freel[POOL_CLASSES];
+	size_t live;
+	int ready;
+} pool;
+
+static int pool_init_locked(lz4e_b200_ctx *ctx, size_t pool_pages)
+{
+	if (pool.ready)
+		return 0;
+	if (!ctx)
+		ctx = lz4e_b200_default_ctx();
+	if (!ctx)
+		return -ENODEV;
+	if (!pool_pages) {
+		const char *e = getenv("LZ4E_CHUNK_POOL_MB");
+		long mb = e ? atol(e) : 1024;
+
+		if (mb < 1)
+			mb = 1;
+		pool_pages = (size_t)mb << (20 - PAGE_SHIFT);
+	}
+	if (lz4e_b200_arena_create(ctx, pool_pages, &pool.arena) != LZ4E_B200_OK)
+		return -ENOMEM;
+	pool.ctx = ctx;
+	pool.base = (uint8_t *)lz4e_b200_arena_pages(pool.arena);
+	pool.npages = pool_pages;
+	pool.bump = 0;
+	pool.live = 0;
+	memset(pool.freel, 0, sizeof(pool.freel));
+	pool.ready = 1;
+	return 0;
+}
+
+int lz4e_chunk_setup(lz4e_b200_ctx *ctx, size_t pool_pages)
+{
+	int rc;
+
+	pthread_mutex_lock(&p_mu);
+	rc = pool_init_locked(ctx, pool_pages);
+	pthread_mutex_unlock(&p_mu);
+	return rc;
+}
+
+void lz4e_chunk_teardown(void)
+{
+	pthread_mutex_lock(&p_mu);
+	if (pool.ready && pool.live == 0) {
+		lz4e_b200_arena_destroy(pool.arena);
+		memset(&pool, 0, sizeof(pool));
+	}
+	pthread_mutex_unlock(&p_mu);
+}
+
+/* `bytes` of zeroed, page-aligned memory; from the pool when it has room, else
+ * plain memory (the codec then bounces it, slower but correct) */
+static void *pool_alloc(size_t bytes, int *from_pool)
+{
+	size_t pages = (bytes + PAGE_SIZE - 1) >> PAGE_SHIFT;
+	void *p = NULL;
+
+	if (!pages)
+		pages = 1;
+	pthread_mutex_lock(&p_mu);
+	if (pool_init_locked(NULL, 0) == 0 && pages < POOL_CLASSES) {
+		if (pool.freel[pages]) {
+			p = pool.freel[pages];
+			pool.freel[pages] = pool.freel[pages]->next;
+		} else if (pool.bump + pages <= pool.npages) {
+			p = pool.base + (pool.bump << PAGE_SHIFT);
+			pool.bump += pages;
+		}
+		if (p)
+			pool.live++;
+	}
+	pthread_mutex_unlock(&p_mu);
+	*from_pool = p != NULL;
+	if (p)
+		return p; /* recycled pinned pages are not cleared: every byte a caller
+			   * may read is written first (copy_from_bio / the codec) */
+	if (posix_memalign(&p, PAGE_SIZE, pages << PAGE_SHIFT))
+		return NULL;
+	memset(p, 0, bytes); /* kzalloc in the reference, lz4e_chunk.c:72,79 */
+	return p;
+}
+
+static void pool_free(void *p, size_t bytes)
+{
+	size_t pages = (bytes + PAGE_SIZE - 1) >> PAGE_SHIFT;
+
+	if (!p)
+		return;
+	if (!pages)
+		pages = 1;
+	pthread_mutex_lock(&p_mu);
+	if (pool.ready && (uint8_t *)p >= pool.base &&
+	    (uint8_t *)p < pool.base + (pool.npages << PAGE_SHIFT)) {
+		struct run_hdr *h = (struct run_hdr *)p;
+
+		h->next = pool.freel[pages];
+		pool.freel[pages] = h;
+		pool.live--;
+		pthread_mutex_unlock(&p_mu);
+		return;
+	}
+	pthread_mutex_unlock(&p_mu);
+	free(p);
+}
+
+static lz4e_b200_ctx *chunk_ctx(void)
+{
+	lz4e_b200_ctx *c;
+
+	pthread_mutex_lock(&p_mu);
+	pool_init_locked(NULL, 0);
+	c = pool.ctx;
+	pthread_mutex_unlock(&p_mu);
+	return c ? c : lz4e_b200_default_ctx();
+}
+
+/* ---- chunks (lz4e_chunk.c:19-107 of the reference) -------------------------- */
+
+void lz4e_buf_copy_from_bio(struct lz4e_buffer *dst, struct bio *src)
+{
+	char *ptr = dst->data;
+	struct bvec_iter it = src->bi_iter;
+
+	while (it.bi_size) {
+		const struct bio_vec *v = &src->bi_io_vec[it.bi_idx];
+		unsigned int take = v->bv_len - it.bi_bvec_done;
+
+		if (take > it.bi_size)
+			take = it.bi_size;
+		memcpy(ptr, (char *)page_address(v->bv_page) + v->bv_offset + it.bi_bvec_done,
+		       take);
+		ptr += take;
+		lz4e_bvec_iter_advance(src->bi_io_vec, &it, take);
+	}
+	dst->data_size = (int)src->bi_iter.bi_size;
+}
+
+void lz4e_chunk_free(struct lz4e_chunk *chunk)
+{
+	if (!chunk)
+		return;
+	pool_free(chunk->src_buf.data, (size_t)chunk->src_buf.buf_size);
+	pool_free(chunk->dst_buf.data, (size_t)chunk->dst_buf.buf_size);
+	free(chunk->wrkmem);
+	free(chunk);
+}
+
+struct lz4e_chunk *lz4e_chunk_alloc(int src_size)
+{
+	const int dst_size = LZ4E_COMPRESSBOUND(src_size);
+	struct lz4e_chunk *chunk;
+	int fp;
+
+	if (src_size < 0)
+		return NULL;
+	chunk = calloc(1, sizeof(*chunk));
+	if (!chunk)
+		return NULL;
+	chunk->src_buf.buf_size = src_size;
+	chunk->src_buf.data = pool_alloc((size_t)src_size, &fp);
+	if (!chunk->src_buf.data)
+		goto free_chunk;
+	chunk->dst_buf.buf_size = dst_size;
+	chunk->dst_buf.data = pool_alloc((size_t)dst_size, &fp);
+	if (!chunk->dst_buf.data)
+		goto free_chunk;
+	/* the GPU keeps its hash table on chip; wrkmem stays part of the chunk
+	 * because LZ4E_compress_default's signature carries it */
+	chunk->wrkmem = calloc(1, LZ4E_MEM_COMPRESS);
+	if (!chunk->wrkmem)
+		goto free_chunk;
+	return chunk;
+
+free_chunk:
+	lz4e_chunk_free(chunk);
+	return NULL;
+}
+
+int lz4e_add_buf_to_bio(struct bio *bio, struct lz4e_buffer *buf)
+{
+	char *data = buf->data;
+	unsigned int left = (unsigned int)buf->buf_size;
+	unsigned int off = (unsigned int)((uintptr_t)data & (PAGE_SIZE - 1));
+	unsigned int len = left < PAGE_SIZE - off ? left : (unsigned int)(PAGE_SIZE - off);
+
+	while (left) {
+		struct bio_vec *v;
+
+		if (bio->bi_vcnt >= bio->bi_max_vecs)
+			return -EAGAIN;
+		v = &bio->bi_io_vec[bio->bi_vcnt++];
+		v->bv_page = (struct page *)((uintptr_t)data & ~(uintptr_t)(PAGE_SIZE - 1));
+		v->bv_len = len;
+		v->bv_offset = off;
+		bio->bi_iter.bi_size += len;
+		data += len;
+		left -= len;
+		off = 0;
+		len = left < PAGE_SIZE ? left : (unsigned int)PAGE_SIZE;
+	}
+	return 0;
+}
+
+/* ---- codec calls, batched (lz4e_chunk.c:109-159 of the reference) ----------- */
+
+/* describe a contiguous buffer as one (multi-page) bio_vec */
+static void buf_to_bvec(const void *p, unsigned int len, struct bio_vec *bv,
+			struct bvec_iter *it)
+{
+	const uintptr_t a = (uintptr_t)p;
+
+	bv->bv_page = (struct page *)(a & ~(uintptr_t)(PAGE_SIZE - 1));
+	bv->bv_offset = (unsigned int)(a & (PAGE_SIZE - 1));
+	bv->bv_len = len ? len : 1;
+	memset(it, 0, sizeof(*it));
+	it->bi_size = len;
+}
+
+struct call_ws {
+	struct lz4e_b200_req *reqs;
+	struct bio_vec *bv;	/* 2 per chunk, for the contiguous forms */
+	struct bvec_iter *it;	/* 2 per chunk: throw-away copies, as
+				 * lz4e_chunk.c:143-144 makes */
+};
+
+static int call_ws_alloc(struct call_ws *w, size_t n)
+{
+	w->reqs = calloc(n, sizeof(*w->reqs));
+	w->bv = calloc(2 * n, sizeof(*w->bv));
+	w->it = calloc(2 * n, sizeof(*w->it));
+	return (w->reqs && w->bv && w->it) ? 0 : -ENOMEM;
+}
+
+static void call_ws_free(struct call_ws *w)
+{
+	free(w->reqs);
+	free(w->bv);
+	free(w->it);
+}
+
+enum { OP_COMPRESS, OP_COMPRESS_EXT, OP_DECOMPRESS };
+
+static int chunk_batch(struct lz4e_chunk **chunks, size_t n, int *status, int op)
+{
+	struct call_ws w;
+	lz4e_b200_ctx *ctx = chunk_ctx();
+	size_t i;
+	int rc;
+
+	if (!n)
+		return 0;
+	if (call_ws_alloc(&w, n)) {
+		call_ws_free(&w);
+		for (i = 0; i < n; i++)
+			status[i] = -ENOMEM;
+		return -ENOMEM;
+	}
+	for (i = 0; i < n; i++) {
+		struct lz4e_chunk *c = chunks[i];
+		struct lz4e_b200_req *q = &w.reqs[i];
+
+		q->src_iter = &w.it[2 * i];
+		q->dst_iter = &w.it[2 * i + 1];
+		switch (op) {
+		case OP_COMPRESS_EXT:
+			q->src = c->src_buf.bio->bi_io_vec;
+			q->dst = c->dst_buf.bio->bi_io_vec;
+			*q->src_iter = c->src_buf.bio->bi_iter;
+			*q->dst_iter = c->dst_buf.bio->bi_iter;
+			break;
+		case OP_COMPRESS:
+			buf_to_bvec(c->src_buf.data, (unsigned int)c->src_buf.data_size,
+				    &w.bv[2 * i], q->src_iter);
+			buf_to_bvec(c->dst_buf.data, (unsigned int)c->dst_buf.buf_size,
+				    &w.bv[2 * i + 1], q->dst_iter);
+			q->src = &w.bv[2 * i];
+			q->dst = &w.bv[2 * i + 1];
+			break;
+		default: /* dst_buf.data -> src_buf.data, lz4e_chunk.c:119-137 */
+			buf_to_bvec(c->dst_buf.data, (unsigned int)c->dst_buf.data_size,
+				    &w.bv[2 * i], q->src_iter);
+			buf_to_bvec(c->src_buf.data, (unsigned int)c->src_buf.buf_size,
+				    &w.bv[2 * i + 1], q->dst_iter);
+			q->src = &w.bv[2 * i];
+			q->dst = &w.bv[2 * i + 1];
+			break;
+		}
+	}
+	if (op == OP_DECOMPRESS)
+		rc = lz4e_b200_decompress_batch(ctx, w.reqs, n, 0);
+	else
+		rc = lz4e_b200_compress_batch(ctx, w.reqs, n, LZ4E_B200_F_KEEP_ITERS);
+	for (i = 0; i < n; i++) {
+		struct lz4e_chunk *c = chunks[i];
+		const int ret = w.reqs[i].ret;
+
+		if (op == OP_DECOMPRESS) {
+			if (rc || ret < 0) { /* lz4e_chunk.c:127-130 */
+				status[i] = -EIO;
+				continue;
+			}
+			if (ret != c->src_buf.buf_size) { /* BUG_ON, lz4e_chunk.c:132 */
+				fprintf(stderr,
+					"lz4e_chunk: decompressed %d bytes, expected %d\n", ret,
+					c->src_buf.buf_size);
+				abort();
+			}
+			c->src_buf.data_size = ret;
+			status[i] = 0;
+		} else {
+			if (rc || !ret) { /* lz4e_chunk.c:114-117, :151-154 */
+				status[i] = -EIO;
+				continue;
+			}
+			c->dst_buf.data_size = ret;
+			status[i] = 0;
+		}
+	}
+	call_ws_free(&w);
+	return rc ? -EIO : 0;
+}
+
+int lz4e_chunk_compress_batch(struct lz4e_chunk **chunks, size_t n, int *status)
+{
+	return chunk_batch(chunks, n, status, OP_COMPRESS);
+}
+
+int lz4e_chunk_compress_ext_batch(struct lz4e_chunk **chunks, size_t n, int *status)
+{
+	return chunk_batch(chunks, n, status, OP_COMPRESS_EXT);
+}
+
+int lz4e_chunk_decompress_batch(struct lz4e_chunk **chunks, size_t n, int *status)
+{
+	return chunk_batch(chunks, n, status, OP_DECOMPRESS);
+}
+
+int lz4e_chunk_compress(struct lz4e_chunk *chunk)
+{
+	int st = -EIO;
+
+	chunk_batch(&chunk, 1, &st, OP_COMPRESS);
+	return st;
+}
+
+int lz4e_chunk_compress_ext(struct lz4e_chunk *chunk)
+{
+	int st = -EIO;
+
+	chunk_batch(&chunk, 1, &st, OP_COMPRESS_EXT);
+	return st;
+}
+
+int lz4e_chunk_decompress(struct lz4e_chunk *chunk)
+{
+	int st = -EIO;
+
+	chunk_batch(&chunk, 1, &st, OP_DECOMPRESS);
+	return st;
+}
+
+/* ---- request path (lz4e_req.c:53-213, lz4e_stats.c:39-52 of the reference) -- */
+
+struct lz4e_dev {
+	uint8_t *store; /* the RAM "underlying device" */
+	uint64_t capacity;
+	struct lz4e_stats read_stats, write_stats;
+	uint64_t compressed_bytes;
+	pthread_mutex_t mu;
+};
+
+struct lz4e_dev *lz4e_dev_create(uint64_t capacity)
+{
+	struct lz4e_dev *dev = calloc(1, sizeof(*dev));
+
+	if (!dev)
+		return NULL;
+	dev->store = calloc(1, capacity ? capacity : 1);
+	if (!dev->store) {
+		free(dev);
+		return NULL;
+	}
+	dev->capacity = capacity;
+	pthread_mutex_init(&dev->mu, NULL);
+	return dev;
+}
+
+void lz4e_dev_destroy(struct lz4e_dev *dev)
+{
+	if (!dev)
+		return;
+	free(dev->store);
+	pthread_mutex_destroy(&dev->mu);
+	free(dev);
+}
+
+/* lz4e_stats_update, lz4e_stats.c:39-52 */
+static void stats_update(struct lz4e_stats *st, int failed, unsigned int vcnt,
+			 unsigned int bytes)
+{
+	st->reqs_total++;
+	if (failed) {
+		st->reqs_failed++;
+		return;
+	}
+	st->vec_count += vcnt;
+	st->data_in_bytes += bytes;
+}
+
+void lz4e_dev_stats(struct lz4e_dev *dev, int write, struct lz4e_stats *out)
+{
+	pthread_mutex_lock(&dev->mu);
+	*out = write ? dev->write_stats : dev->read_stats;
+	pthread_mutex_unlock(&dev->mu);
+}
+
+void lz4e_dev_stats_reset(struct lz4e_dev *dev)
+{
+	pthread_mutex_lock(&dev->mu);
+	memset(&dev->read_stats, 0, sizeof(dev->read_stats));
+	memset(&dev->write_stats, 0, sizeof(dev->write_stats));
+	dev->compressed_bytes = 0;
+	pthread_mutex_unlock(&dev->mu);
+}
+
+uint64_t lz4e_dev_compressed_bytes(struct lz4e_dev *dev)
+{
+	return dev->compressed_bytes;
+}
+
+/* lz4e_bio_bytes_to_pages, lz4e_req.c:77-82 */
+static unsigned short bytes_to_pages(size_t bytes)
+{
+	size_t pages = (bytes + PAGE_SIZE - 1) / PAGE_SIZE;
+
+	return (unsigned short)(pages < BIO_MAX_VECS ? pages : BIO_MAX_VECS);
+}
+
+struct wreq {
+	struct lz4e_chunk *chunk;
+	struct bio new_bio;
+	struct bio_vec *vecs;
+};
+
+int lz4e_dev_submit_writes(struct lz4e_dev *dev, struct bio **bios, size_t n, int *status)
+{
+	struct wreq *w = calloc(n ? n : 1, sizeof(*w));
+	struct lz4e_chunk **live = calloc(n ? n : 1, sizeof(*live));
+	size_t *map = calloc(n ? n : 1, sizeof(*map));
+	int *st = calloc(n ? n : 1, sizeof(*st));
+	size_t i, k, nlive = 0;
+
+	if (!w || !live || !map || !st) {
+		for (i = 0; i < n; i++)
+			status[i] = -ENOMEM;
+		goto out;
+	}
+	/* lz4e_write_req_init up to the codec call, lz4e_req.c:153-175 */
+	for (i = 0; i < n; i++) {
+		struct bio *ob = bios[i];
+		const unsigned int size = ob->bi_iter.bi_size;
+		const uint64_t pos = (uint64_t)ob->bi_iter.bi_sector * 512u;
+		unsigned short nv;
+
+		status[i] = 0;
+		if (pos + size > dev->capacity || pos + size < pos) {
+			status[i] = -ERANGE;
+			continue;
+		}
+		w[i].chunk = lz4e_chunk_alloc((int)size);
+		if (!w[i].chunk) {
+			status[i] = -ENOMEM;
+			continue;
+		}
+		nv = bytes_to_pages((size_t)w[i].chunk->dst_buf.buf_size + PAGE_SIZE);
+		w[i].vecs = calloc(nv ? nv : 1, sizeof(*w[i].vecs));
+		if (!w[i].vecs) {
+			status[i] = -ENOMEM;
+			continue;
+		}
+		w[i].new_bio.bi_io_vec = w[i].vecs;
+		w[i].new_bio.bi_max_vecs = nv;
+		w[i].new_bio.bi_opf = ob->bi_opf;
+		w[i].new_bio.bi_iter.bi_sector = ob->bi_iter.bi_sector;
+		if (lz4e_add_buf_to_bio(&w[i].new_bio, &w[i].chunk->dst_buf)) {
+			status[i] = -EIO; /* BLK_STS_IOERR, lz4e_req.c:169-173 */
+			continue;
+		}
+		w[i].chunk->src_buf.bio = ob;
+		w[i].chunk->dst_buf.bio = &w[i].new_bio;
+		map[nlive] = i;
+		live[nlive++] = w[i].chunk;
+	}
+	/* compress every bio as one block, then decompress it again
+	 * (lz4e_req.c:177-189), each step ONE GPU batch */
+	lz4e_chunk_compress_ext_batch(live, nlive, st);
+	for (k = 0, i = 0; k < nlive; k++) {
+		if (st[k]) {
+			status[map[k]] = st[k];
+			continue;
+		}
+		map[i] = map[k];
+		live[i++] = live[k];
+	}
+	nlive = i;
+	lz4e_chunk_decompress_batch(live, nlive, st);
+	pthread_mutex_lock(&dev->mu);
+	for (k = 0; k < nlive; k++) {
+		struct bio *ob = bios[map[k]];
+		struct lz4e_chunk *c = live[k];
+
+		if (st[k]) {
+			status[map[k]] = st[k];
+			continue;
+		}
+		/* the new bio is reset and loaded with the DECOMPRESSED buffer
+		 * (lz4e_req.c:191-199); the RAM device takes its bytes */
+		memcpy(dev->store + (uint64_t)ob->bi_iter.bi_sector * 512u, c->src_buf.data,
+		       (size_t)c->src_buf.data_size);
+		dev->compressed_bytes += (uint64_t)c->dst_buf.data_size;
+	}
+	for (i = 0; i < n; i++)
+		stats_update(&dev->write_stats, status[i] != 0,
+			     bytes_to_pages(bios[i]->bi_iter.bi_size), bios[i]->bi_iter.bi_size);
+	pthread_mutex_unlock(&dev->mu);
+out:
+	for (i = 0; w && i < n; i++) {
+		lz4e_chunk_free(w[i].chunk);
+		free(w[i].vecs);
+	}
+	free(w);
+	free(live);
+	free(map);
+	free(st);
+	return 0;
+}
+
+int lz4e_dev_submit_reads(struct lz4e_dev *dev, struct bio **bios, size_t n, int *status)
+{
+	size_t i;
+
+	pthread_mutex_lock(&dev->mu);
+	for (i = 0; i < n; i++) {
+		struct bio *b = bios[i];
+		struct bvec_iter it = b->bi_iter;
+		const uint64_t pos = (uint64_t)it.bi_sector * 512u;
+		const uint8_t *from = dev->store + pos;
+
+		status[i] = 0;
+		if (pos + it.bi_size > dev->capacity || pos + it.bi_size < pos) {
+			status[i] = -ERANGE;
+			stats_update(&dev->read_stats, 1, 0, 0);
+			continue;
+		}
+		while (it.bi_size) {
+			const struct bio_vec *v = &b->bi_io_vec[it.bi_idx];
+			unsigned int take = v->bv_len - it.bi_bvec_done;
+
+			if (take > it.bi_size)
+				take = it.bi_size;
+			memcpy((char *)page_address(v->bv_page) + v->bv_offset + it.bi_bvec_done,
+			       from, take);
+			from += take;
+			lz4e_bvec_iter_advance(b->bi_io_vec, &it, take);
+		}
+		stats_update(&dev->read_stats, 0, b->bi_vcnt, b->bi_iter.bi_size);
+	}
+	pthread_mutex_unlock(&dev->mu);
+	return 0;
+}
