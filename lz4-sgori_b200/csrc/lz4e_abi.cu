@@ -41,6 +41,15 @@ struct lz4e_b200_ctx {
 	std::atomic<uint64_t> launches;
 	uint8_t *scratch;
 	size_t scratch_bytes;
+	/* input slots of the GIN compress kernels, one buffer per stream in use */
+	struct cslot {
+		cudaStream_t stream;
+		uint8_t *p;
+		size_t bytes;
+	};
+	std::vector<cslot> cscratch;
+	int gin_min;	 /* blocks above this many bytes use the GIN compress kernels */
+	int gin_per_sm;	 /* resident warps per SM for them (0: as many as fit) */
 	std::mutex mu;
 	std::vector<lz4e_b200_arena *> arenas;
 	char err[256];
@@ -123,11 +132,17 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 	if (const char *e = getenv("LZ4E_B200_DGROUP")) {
 		int g = atoi(e);
 
-		if (g == 8 || g == 16 || g == 32)
+		if (g == 2 || g == 4 || g == 8 || g == 16 || g == 32)
 			ctx->dgroup = g;
 	}
 	if (const char *e = getenv("LZ4E_B200_DSTAGE"))
 		ctx->dstage = atoi(e) ? 1 : 0;
+	ctx->gin_min = 12288;
+	ctx->gin_per_sm = 0;
+	if (const char *e = getenv("LZ4E_B200_GIN_MIN"))
+		ctx->gin_min = atoi(e);
+	if (const char *e = getenv("LZ4E_B200_GIN_PER_SM"))
+		ctx->gin_per_sm = atoi(e);
 	if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
 	    cudaMalloc((void **)&ctx->d_ctl, CTL_WORDS * sizeof(uint32_t)) != cudaSuccess ||
 	    cudaMemset(ctx->d_ctl, 0, CTL_WORDS * sizeof(uint32_t)) != cudaSuccess) {
@@ -147,6 +162,8 @@ void lz4e_b200_ctx_destroy(lz4e_b200_ctx *ctx)
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
 	cudaFree(ctx->scratch);
+	for (auto &c : ctx->cscratch)
+		cudaFree(c.p);
 	cudaFree(ctx->d_ctl);
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
@@ -430,6 +447,38 @@ static int ensure_scratch(lz4e_b200_ctx *ctx, size_t bytes)
 	return LZ4E_B200_OK;
 }
 
+/* input slots for a GIN compress launch on stream s (kept per stream, so
+ * launches on different streams never share slots) */
+static uint8_t *compress_slots(lz4e_b200_ctx *ctx, cudaStream_t s, size_t bytes)
+{
+	std::lock_guard<std::mutex> lk(ctx->mu);
+
+	for (auto &c : ctx->cscratch) {
+		if (c.stream != s)
+			continue;
+		if (c.bytes >= bytes)
+			return c.p;
+		if (cudaStreamSynchronize(s) != cudaSuccess)
+			return nullptr;
+		cudaFree(c.p);
+		c.p = nullptr;
+		c.bytes = 0;
+		if (cudaMalloc((void **)&c.p, bytes) != cudaSuccess) {
+			c.p = nullptr;
+			return nullptr;
+		}
+		c.bytes = bytes;
+		return c.p;
+	}
+	lz4e_b200_ctx::cslot c = { s, nullptr, 0 };
+
+	if (cudaMalloc((void **)&c.p, bytes) != cudaSuccess)
+		return nullptr;
+	c.bytes = bytes;
+	ctx->cscratch.push_back(c);
+	return c.p;
+}
+
 /* internal helpers for the other translation units */
 uint8_t *lz4e_ctx_scratch(lz4e_b200_ctx *ctx, size_t bytes)
 {
@@ -456,7 +505,7 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 		return LZ4E_B200_OK;
 	if (max_in_bytes > 65536u) {
 		set_err(ctx, "blocks above 65536 bytes (%u) are not supported by the "
-			     "shared-memory compressor yet", max_in_bytes);
+			     "compressor yet (16-bit table positions)", max_in_bytes);
 		return LZ4E_B200_EINVAL;
 	}
 	cudaSetDevice(ctx->device);
@@ -487,11 +536,36 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 		if (flags & LZ4E_B200_DEV_DST_LINEAR)
 			a.out_cap = 64u;
 	}
-	if (lz4e_launch_compress(&a, (flags & LZ4E_B200_DEV_DST_LINEAR) ? 1 : 0, ctx->sm_count, s,
-				 nullptr)) {
-		set_err(ctx, "compress launch failed: %s",
-			cudaGetErrorString(cudaGetLastError()));
-		return LZ4E_B200_EIO;
+	{
+		/* large blocks: input in a global slot read through L1 instead of
+		 * shared memory (64 KiB blocks: 3 -> 16 resident warps per SM) */
+		const int direct = (flags & LZ4E_B200_DEV_DST_LINEAR) ? 1 : 0;
+		const int gin = (int)max_in_bytes > ctx->gin_min;
+		int grid = 0;
+		size_t smem = 0;
+
+		a.in_scratch = nullptr;
+		a.in_stride = 0;
+		if (lz4e_compress_plan(&a, direct, gin, ctx->sm_count, gin ? ctx->gin_per_sm : 0,
+				       &grid, &smem)) {
+			set_err(ctx, "compress launch plan failed: %s",
+				cudaGetErrorString(cudaGetLastError()));
+			return LZ4E_B200_EIO;
+		}
+		if (gin) {
+			a.in_stride = ((a.in_cap + 63u) & ~255u) + 256u;
+			a.in_scratch = compress_slots(ctx, s, (size_t)grid * a.in_stride + 256);
+			if (!a.in_scratch) {
+				set_err(ctx, "compress input slots (%zu bytes): out of device memory",
+					(size_t)grid * a.in_stride);
+				return LZ4E_B200_ENOMEM;
+			}
+		}
+		if (lz4e_launch_compress(&a, direct, gin, grid, smem, s)) {
+			set_err(ctx, "compress launch failed: %s",
+				cudaGetErrorString(cudaGetLastError()));
+			return LZ4E_B200_EIO;
+		}
 	}
 	ctx->launches++;
 	return LZ4E_B200_OK;

@@ -62,13 +62,19 @@ struct lz4e_compress_args {
 	uint32_t table_bytes; /* 16384, or 8192 when no block can select byU16 */
 	uint32_t in_cap;  /* bytes of input staging (multiple of 16) */
 	uint32_t out_cap; /* bytes of output staging (multiple of 16, >= 1024) */
+	/* GIN kernels only: the block is gathered into a linear slot in global
+	 * memory (one slot per resident warp) and read back through L1, so that
+	 * shared memory holds just the hash table and large blocks no longer
+	 * limit the number of resident warps */
+	uint8_t *in_scratch;
+	uint32_t in_stride; /* bytes per slot, >= in_cap + 64 */
 };
 
-/* shared memory needed by one warp */
+/* shared memory needed by one warp (in_cap = 0 for the GIN kernels) */
 static inline uint32_t lz4e_compress_smem_bytes(uint32_t table_bytes,
 						uint32_t in_cap, uint32_t out_cap)
 {
-	return table_bytes + in_cap + LZ4E_K_PAD + out_cap + LZ4E_K_PAD;
+	return table_bytes + (in_cap ? in_cap + LZ4E_K_PAD : 0u) + out_cap + LZ4E_K_PAD;
 }
 
 /* number of bytes advanced after k search visits: visit k uses step 1 for
@@ -164,7 +170,7 @@ LZ4E_DEV void lz4e_put_run(uint8_t *p, uint32_t count, uint32_t last,
  * Returns the reference's return value; src_end/dst_end receive the iterator
  * end state.
  */
-template <int TT, bool DIRECT>
+template <int TT, bool DIRECT, bool GIN>
 LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				      const struct lz4e_b200_dev_iter &di,
 				      const uint8_t *d, uint32_t n, uint8_t *sm,
@@ -175,7 +181,10 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 	uint16_t *tab = reinterpret_cast<uint16_t *>(sm);
 	int32_t ret = 0;
 
-	LZ4E_ASSUME_SHARED(d);
+	if (GIN)
+		LZ4E_ASSUME_GLOBAL(d);
+	else
+		LZ4E_ASSUME_SHARED(d);
 	LZ4E_ASSUME_SHARED(sm);
 	if (!DIRECT)
 		LZ4E_ASSUME_SHARED(out_area);
@@ -183,7 +192,10 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 	const uint32_t dm = (uint32_t)(uintptr_t)d & 3u;
 	const uint8_t *da = d - dm;
 
-	LZ4E_ASSUME_SHARED(da);
+	if (GIN)
+		LZ4E_ASSUME_GLOBAL(da);
+	else
+		LZ4E_ASSUME_SHARED(da);
 
 	{
 		const bool limited = cap < n + n / 255u + 16u; /* :553 */
@@ -618,15 +630,16 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
  * Compress block b.  sm points at this warp's shared memory
  * (lz4e_compress_smem_bytes()).  All 32 lanes call it together.
  */
-template <bool DIRECT>
+template <bool DIRECT, bool GIN>
 LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
-				  uint8_t *sm, uint32_t lane)
+				  uint8_t *sm, uint32_t lane, uint32_t slot)
 {
 	const struct lz4e_b200_dev_iter si = a.src_iters[b];
 	const struct lz4e_b200_dev_iter di = a.dst_iters[b];
 	const uint32_t n = si.bi_size;
-	uint8_t *in_area = sm + a.table_bytes;
-	uint8_t *out_area = in_area + a.in_cap + LZ4E_K_PAD;
+	uint8_t *in_area = GIN ? a.in_scratch + (size_t)slot * a.in_stride
+			       : sm + a.table_bytes;
+	uint8_t *out_area = sm + a.table_bytes + (GIN ? 0u : a.in_cap + LZ4E_K_PAD);
 	const uint8_t *d; /* d[pos] = source byte at linear position pos */
 	int tt = LZ4E_TT_U16;
 	int32_t ret = 0;
@@ -691,15 +704,15 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 
 	switch (tt) {
 	case LZ4E_TT_U16:
-		ret = lz4e_compress_encode<LZ4E_TT_U16, DIRECT>(a, di, d, n, sm, out_area, lane,
+		ret = lz4e_compress_encode<LZ4E_TT_U16, DIRECT, GIN>(a, di, d, n, sm, out_area, lane,
 							src_end, dst_end);
 		break;
 	case LZ4E_TT_U32:
-		ret = lz4e_compress_encode<LZ4E_TT_U32, DIRECT>(a, di, d, n, sm, out_area, lane,
+		ret = lz4e_compress_encode<LZ4E_TT_U32, DIRECT, GIN>(a, di, d, n, sm, out_area, lane,
 							src_end, dst_end);
 		break;
 	default:
-		ret = lz4e_compress_encode<LZ4E_TT_U64, DIRECT>(a, di, d, n, sm, out_area, lane,
+		ret = lz4e_compress_encode<LZ4E_TT_U64, DIRECT, GIN>(a, di, d, n, sm, out_area, lane,
 							src_end, dst_end);
 		break;
 	}
@@ -717,9 +730,9 @@ done:
 }
 
 /* persistent loop: warps pull block indices from a global counter */
-template <bool DIRECT>
+template <bool DIRECT, bool GIN>
 LZ4E_DEV void lz4e_compress_warp(const lz4e_compress_args &a, uint8_t *sm,
-				 uint32_t lane)
+				 uint32_t lane, uint32_t slot)
 {
 	for (;;) {
 		uint32_t b = 0;
@@ -729,7 +742,7 @@ LZ4E_DEV void lz4e_compress_warp(const lz4e_compress_args &a, uint8_t *sm,
 		b = lz4e_shfl(LZ4E_FULL, b, 0);
 		if (b >= a.nblocks)
 			break;
-		lz4e_compress_block<DIRECT>(a, b, sm, lane);
+		lz4e_compress_block<DIRECT, GIN>(a, b, sm, lane, slot);
 	}
 }
 

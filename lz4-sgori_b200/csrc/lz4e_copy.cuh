@@ -111,8 +111,8 @@ LZ4E_DEV void lz4e_copy(uint8_t *dst, const uint8_t *src, uint32_t len,
 		const uint8_t *al = (const uint8_t *)(sa & ~(uintptr_t)3);
 		const uint32_t sh = (uint32_t)(sa & 3) * 8;
 
-		if (l < head)
-			dst[l] = src[l];
+		for (uint32_t i = l; i < head; i += W) /* head <= 3 */
+			dst[i] = src[i];
 		if (sh == 0) {
 			for (uint32_t i = l; i < body; i += W)
 				lz4e_st32a(dst + head + ((size_t)i << 2),

@@ -54,6 +54,7 @@ struct lz4e_decompress_args {
 	uint32_t scratch_stride; /* bytes per slot */
 };
 
+
 /* forward-only view of the compressed SG stream: byte p lives at bias[p]
  * while lo <= p < hi */
 struct lz4e_in_view {

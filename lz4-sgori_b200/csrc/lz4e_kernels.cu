@@ -13,11 +13,11 @@
 extern __shared__ __align__(16) uint8_t lz4e_smem[];
 
 /* ---- K2: compression, one warp (= one CTA) per block in flight ----------- */
-template <bool DIRECT>
+template <bool DIRECT, bool GIN>
 __global__ void __launch_bounds__(32)
 lz4e_compress_kernel(const lz4e_compress_args a)
 {
-	lz4e_compress_warp<DIRECT>(a, lz4e_smem, threadIdx.x);
+	lz4e_compress_warp<DIRECT, GIN>(a, lz4e_smem, threadIdx.x, blockIdx.x);
 }
 
 /* ---- K4: decompression, LZ4E_D_WARPS warps per CTA, 32/GS blocks per warp */
@@ -75,13 +75,36 @@ static int lz4e_set_smem(const void *fn, size_t bytes)
 		       : -1;
 }
 
-int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int sm_count,
-			 cudaStream_t stream, int *grid_out)
-{
-	const size_t smem = lz4e_compress_smem_bytes(a->table_bytes, a->in_cap, a->out_cap);
-	int per_sm = 0;
-	auto fn = direct ? lz4e_compress_kernel<true> : lz4e_compress_kernel<false>;
+typedef void (*lz4e_compress_fn)(const lz4e_compress_args);
 
+static lz4e_compress_fn compress_fn(int direct, int gin)
+{
+	if (gin)
+		return direct ? lz4e_compress_kernel<true, true> : lz4e_compress_kernel<false, true>;
+	return direct ? lz4e_compress_kernel<true, false> : lz4e_compress_kernel<false, false>;
+}
+
+/*
+ * Grid and shared-memory size of a compress launch: one persistent one-warp
+ * CTA per block in flight, as many per SM as shared memory allows, at most
+ * max_per_sm when that is > 0 (the GIN kernels read their input through L1,
+ * which shares the SM's 256 KB with shared memory: fewer, better cached warps
+ * can beat more warps).
+ */
+int lz4e_compress_plan(const lz4e_compress_args *a, int direct, int gin, int sm_count,
+		       int max_per_sm, int *grid_out, size_t *smem_out)
+{
+	size_t smem = lz4e_compress_smem_bytes(a->table_bytes, gin ? 0u : a->in_cap, a->out_cap);
+	int per_sm = 0;
+	lz4e_compress_fn fn = compress_fn(direct, gin);
+
+	if (max_per_sm > 0) {
+		/* ask for enough shared memory that only max_per_sm CTAs fit */
+		const size_t want = ((size_t)227 * 1024 / (size_t)max_per_sm - 1024) & ~(size_t)127;
+
+		if (want > smem)
+			smem = want;
+	}
 	if (lz4e_set_smem((const void *)fn, smem))
 		return -1;
 	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 32, smem) !=
@@ -94,9 +117,17 @@ int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int sm_count,
 		grid = a->nblocks;
 	if (grid < 1)
 		grid = 1;
+	*grid_out = (int)grid;
+	*smem_out = smem;
+	return 0;
+}
+
+int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int gin, int grid,
+			 size_t smem, cudaStream_t stream)
+{
+	lz4e_compress_fn fn = compress_fn(direct, gin);
+
 	fn<<<(unsigned)grid, 32, smem, stream>>>(*a);
-	if (grid_out)
-		*grid_out = (int)grid;
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
@@ -143,7 +174,9 @@ int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_co
 		     : group == 16 ? (const void *)lz4e_decompress_kernel<16, true>
 				   : (const void *)lz4e_decompress_kernel<32, true>;
 	else
-		fn = group == 8    ? (const void *)lz4e_decompress_kernel<8, false>
+		fn = group == 2	   ? (const void *)lz4e_decompress_kernel<2, false>
+		     : group == 4  ? (const void *)lz4e_decompress_kernel<4, false>
+		     : group == 8  ? (const void *)lz4e_decompress_kernel<8, false>
 		     : group == 16 ? (const void *)lz4e_decompress_kernel<16, false>
 				   : (const void *)lz4e_decompress_kernel<32, false>;
 	if (lz4e_set_smem(fn, smem))
@@ -170,6 +203,10 @@ int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
 		}
 	}
 	switch (group) {
+	case 2:
+		return launch_decompress_t<2, false>(a, sm_count, stream, grid_limit, grid_out);
+	case 4:
+		return launch_decompress_t<4, false>(a, sm_count, stream, grid_limit, grid_out);
 	case 8:
 		return launch_decompress_t<8, false>(a, sm_count, stream, grid_limit, grid_out);
 	case 16:

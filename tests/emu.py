@@ -23,7 +23,7 @@ def load():
     lib = ctypes.CDLL(SIMT_SO)
     vp, u32 = ctypes.c_void_p, ctypes.c_uint32
     lib.simt_compress_batch.restype = ctypes.c_int
-    lib.simt_compress_batch.argtypes = [vp, vp, vp, vp, u32, u32, u32, u32, vp, vp, vp, u32]
+    lib.simt_compress_batch.argtypes = [vp, vp, vp, vp, u32, u32, u32, u32, vp, vp, vp, u32, u32]
     lib.simt_decompress_batch.restype = ctypes.c_int
     lib.simt_decompress_batch.argtypes = [vp, vp, vp, vp, u32, u32, u32, vp, vp, vp, u32, u32]
     return lib
@@ -47,7 +47,8 @@ def _p(a):
     return ctypes.c_void_p(a.ctypes.data) if a is not None else None
 
 
-def compress(lib, src_layout, dst_layout, in_cap=4096, out_cap=4352, seed=1, table_bytes=16384):
+def compress(lib, src_layout, dst_layout, in_cap=4096, out_cap=4352, seed=1, table_bytes=16384,
+             gin=False):
     sbv, sit = to_dev(src_layout)
     dbv, dit = to_dev(dst_layout)
     n = len(sit)
@@ -55,7 +56,7 @@ def compress(lib, src_layout, dst_layout, in_cap=4096, out_cap=4352, seed=1, tab
     ends = np.zeros(n, dtype=DEV_END)
     faults = np.zeros(1, dtype=np.uint32)
     rc = lib.simt_compress_batch(_p(sbv), _p(sit), _p(dbv), _p(dit), n, table_bytes, in_cap, out_cap,
-                                 _p(rets), _p(ends), _p(faults), seed)
+                                 _p(rets), _p(ends), _p(faults), seed, 1 if gin else 0)
     assert rc == 0
     return rets, ends, int(faults[0])
 

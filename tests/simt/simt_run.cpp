@@ -205,12 +205,15 @@ int simt_compress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 			const lz4e_b200_dev_iter *dst_iters, uint32_t nblocks,
 			uint32_t table_bytes, uint32_t in_cap, uint32_t out_cap,
 			int32_t *rets, lz4e_b200_dev_end *ends, uint32_t *faults,
-			uint32_t seed)
+			uint32_t seed, uint32_t gin)
 {
 	lz4e_compress_args a;
 	uint32_t counter = 0;
-	const uint32_t bytes = lz4e_compress_smem_bytes(table_bytes, in_cap, out_cap);
+	const uint32_t bytes = lz4e_compress_smem_bytes(table_bytes, gin ? 0u : in_cap, out_cap);
 	void *smraw = nullptr;
+	/* GIN: the block is gathered into a global slot (stale garbage in it, as on
+	 * the GPU when the slot is reused) */
+	std::vector<uint8_t> slot(gin ? in_cap + 512 : 0, 0xA7);
 
 	if (posix_memalign(&smraw, 1024, bytes + 64))
 		return -1;
@@ -227,14 +230,20 @@ int simt_compress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 	a.table_bytes = table_bytes;
 	a.in_cap = in_cap;
 	a.out_cap = out_cap;
+	a.in_scratch = gin ? slot.data() : nullptr;
+	a.in_stride = gin ? in_cap + 256 : 0;
 	uint8_t *sm = (uint8_t *)smraw;
 
 	/* out_cap 64 = what lz4e_b200_compress_dev passes for linear destinations:
 	 * output written in place, no staging */
-	if (out_cap == 64)
-		simt::run_warp([&](uint32_t lane) { lz4e_compress_warp<true>(a, sm, lane); }, seed);
+	if (out_cap == 64 && gin)
+		simt::run_warp([&](uint32_t lane) { lz4e_compress_warp<true, true>(a, sm, lane, 0); }, seed);
+	else if (out_cap == 64)
+		simt::run_warp([&](uint32_t lane) { lz4e_compress_warp<true, false>(a, sm, lane, 0); }, seed);
+	else if (gin)
+		simt::run_warp([&](uint32_t lane) { lz4e_compress_warp<false, true>(a, sm, lane, 0); }, seed);
 	else
-		simt::run_warp([&](uint32_t lane) { lz4e_compress_warp<false>(a, sm, lane); }, seed);
+		simt::run_warp([&](uint32_t lane) { lz4e_compress_warp<false, false>(a, sm, lane, 0); }, seed);
 	free(smraw);
 	return 0;
 }
@@ -272,6 +281,12 @@ int simt_decompress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 	simt::run_warp(
 		[&](uint32_t lane) {
 			switch (group) {
+			case 2:
+				lz4e_decompress_warp<2>(a, sm, 0, lane);
+				break;
+			case 4:
+				lz4e_decompress_warp<4>(a, sm, 0, lane);
+				break;
 			case 8:
 				lz4e_decompress_warp<8>(a, sm, 0, lane);
 				break;

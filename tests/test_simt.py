@@ -39,14 +39,15 @@ def _cases():
 
 
 # streamed output / whole block staged / written in place (linear destination)
-@pytest.mark.parametrize("out_cap", [1024, 16384, 64])
-def test_compress_body_matches_oracle(simt, ref_lib, out_cap):
+@pytest.mark.parametrize("out_cap,gin", [(1024, False), (16384, False), (64, False),
+                                         (1024, True), (64, True)])
+def test_compress_body_matches_oracle(simt, ref_lib, out_cap, gin):
     datas, specs = _cases()
     src = _host_layout(specs, datas)
     dspecs = [sg.segs_single(sg.compress_bound(len(d))) for d in datas]
     dst = _host_layout(dspecs)
     dst.arena.mem[:] = 0xEE
-    rets, ends, faults = emu.compress(simt, src, dst, in_cap=12288, out_cap=out_cap)
+    rets, ends, faults = emu.compress(simt, src, dst, in_cap=12288, out_cap=out_cap, gin=gin)
     ref_dst, (ref_rets, _, so, do) = common.oracle_compress(ref_lib, src, dspecs, want_iters=True)
     assert faults == 0
     assert np.array_equal(rets, ref_rets)
@@ -76,7 +77,7 @@ def test_compress_body_limited_output(simt, ref_lib, out_cap):
         assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
 
 
-@pytest.mark.parametrize("group", [8, 16, 32])
+@pytest.mark.parametrize("group", [2, 4, 8, 16, 32])
 def test_decompress_body_roundtrip(simt, ref_lib, group):
     datas, specs = _cases()
     keep = [i for i, d in enumerate(datas) if len(d) > 0]
