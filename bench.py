@@ -246,12 +246,12 @@ def run_ours(args):
                 t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, flags=pkg.DEV_DST_LINEAR, stream=sp),
                 stream))
             evs.append(event_ms(torch, lambda: ctx.decompress_dev(
-                t[2], d_cit, t[4], t[5], nb, max_c, BLOCK, d_rets2, flags=pkg.DEV_DST_LINEAR,
-                stream=sp), stream))
+                t[2], d_cit, t[4], t[5], nb, max_c, BLOCK, d_rets2,
+                flags=pkg.DEV_DST_LINEAR | pkg.DEV_SRC_LINEAR, stream=sp), stream))
         else:
             ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, flags=pkg.DEV_DST_LINEAR, stream=sp)
             ctx.decompress_dev(t[2], d_cit, t[4], t[5], nb, max_c, BLOCK, d_rets2,
-                               flags=pkg.DEV_DST_LINEAR, stream=sp)
+                               flags=pkg.DEV_DST_LINEAR | pkg.DEV_SRC_LINEAR, stream=sp)
 
     for _ in range(max(args.warmup, 3)):
         step()

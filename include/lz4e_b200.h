@@ -102,6 +102,10 @@ int lz4e_b200_sync(lz4e_b200_ctx *ctx, void *stream);
 				     * segment holding the whole capacity:
 				     * decompress needs no scratch, compress
 				     * writes in place without staging */
+#define LZ4E_B200_DEV_SRC_LINEAR 4u /* decompress: every compressed block is
+				     * one contiguous segment (no gather slot
+				     * is reserved for the lane-per-block
+				     * decoder) */
 
 /*
  * LZ4E_compress_default for `nblocks` independent blocks.

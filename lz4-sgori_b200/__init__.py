@@ -27,7 +27,7 @@ REQ = np.dtype([("src", "<u8"), ("dst", "<u8"), ("src_iter", "<u8"), ("dst_iter"
                 ("ret", "<i4"), ("rsvd", "<i4")])
 
 F_SRC_RESIDENT, F_DST_ON_DEVICE, F_KEEP_ITERS, F_DST_PRESERVE = 1, 2, 4, 8
-DEV_NO_BYU16, DEV_DST_LINEAR = 1, 2
+DEV_NO_BYU16, DEV_DST_LINEAR, DEV_SRC_LINEAR = 1, 2, 4
 
 
 class Lz4eError(RuntimeError):

@@ -132,7 +132,7 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 	if (const char *e = getenv("LZ4E_B200_DGROUP")) {
 		int g = atoi(e);
 
-		if (g == 2 || g == 4 || g == 8 || g == 16 || g == 32)
+		if (g == 1 || g == 2 || g == 4 || g == 8 || g == 16 || g == 32)
 			ctx->dgroup = g;
 	}
 	if (const char *e = getenv("LZ4E_B200_DSTAGE"))
@@ -582,12 +582,19 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 	lz4e_decompress_args a;
 	cudaStream_t s;
 	int stage, grid_limit = 0;
-	/* lanes per block: 8 for the 4 KiB chunk size, 16 for large blocks
-	 * (measured on B200: 64 KiB blocks 106 -> 130 GB/s; 4 KiB 290 vs 225) */
-	const int group = (ctx && ctx->dgroup) ? ctx->dgroup
-						: (max_out_bytes > 8192u ? 16 : 8);
+	/*
+	 * lanes per block: 8 for the 4 KiB chunk size, 16 for large blocks
+	 * (measured on B200: 64 KiB blocks 106 -> 130 GB/s; 4 KiB 290 vs 225).
+	 * Small blocks in batches large enough to give every resident lane a
+	 * block of its own go to the lane-per-block decoder ("1"; 4 KiB mixed
+	 * 290 -> 325 GB/s at 262144 blocks, but 140 vs 232 GB/s at 65536).
+	 */
+	int group = (ctx && ctx->dgroup) ? ctx->dgroup : (max_out_bytes > 8192u ? 16 : 8);
 
-	(void)max_in_bytes;
+	if (ctx && !ctx->dgroup && max_out_bytes <= 8192u &&
+	    nblocks >= (uint32_t)ctx->sm_count * 24u * 32u)
+		group = 1;
+
 	if (!ctx)
 		return LZ4E_B200_ENODEV;
 	if (nblocks == 0)
@@ -612,8 +619,53 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 	a.stage_cap = stage ? (((max_out_bytes + 15u) & ~15u) + 16u) : 0u;
 	a.scratch = nullptr;
 	a.scratch_stride = 0;
-	if (!stage && !(flags & LZ4E_B200_DEV_DST_LINEAR)) {
-		/* one linear slot per resident group for scattered destinations */
+	a.in_scratch = nullptr;
+	a.in_stride = 0;
+	if (group == 1) {
+		/* lane-per-block decoder: one output slot per resident lane unless
+		 * every destination is contiguous, one input slot unless every
+		 * source is */
+		const uint32_t ostride =
+			(flags & LZ4E_B200_DEV_DST_LINEAR) ? 0u : ((max_out_bytes + 255u) & ~255u);
+		const uint32_t istride =
+			(flags & LZ4E_B200_DEV_SRC_LINEAR) ? 0u : ((max_in_bytes + 255u) & ~255u);
+		const size_t per_cta = (size_t)LZ4E_D_WARPS * 32 * ((size_t)ostride + istride);
+
+		stage = 0;
+		a.stage_cap = 0;
+		if (per_cta) {
+			int grid = lz4e_decompress_max_grid(1, 0, 0, ctx->sm_count);
+			const size_t budget = (size_t)6 << 30;
+			const long long want =
+				((long long)nblocks + LZ4E_D_WARPS * 32 - 1) / (LZ4E_D_WARPS * 32);
+
+			if (grid < 1) {
+				set_err(ctx, "decompress occupancy query failed");
+				return LZ4E_B200_EIO;
+			}
+			if (grid > want)
+				grid = (int)want;
+			if ((size_t)grid * per_cta > budget) {
+				grid = (int)(budget / per_cta);
+				if (grid < 1)
+					grid = 1;
+			}
+			grid_limit = grid;
+			int rc = ensure_scratch(ctx, (size_t)grid * per_cta);
+
+			if (rc)
+				return rc;
+			if (ostride) {
+				a.scratch = ctx->scratch;
+				a.scratch_stride = ostride;
+			}
+			if (istride) {
+				a.in_scratch = ctx->scratch +
+					       (size_t)grid * LZ4E_D_WARPS * 32 * ostride;
+				a.in_stride = istride;
+			}
+		}
+	} else if (!stage && !(flags & LZ4E_B200_DEV_DST_LINEAR)) {		/* one linear slot per resident group for scattered destinations */
 		const uint32_t stride = (max_out_bytes + 255u) & ~255u;
 		int grid = lz4e_decompress_max_grid(group, 0, 0, ctx->sm_count);
 		const size_t per_cta = (size_t)LZ4E_D_WARPS * (32 / group) * stride;

@@ -52,6 +52,10 @@ struct lz4e_decompress_args {
 	uint32_t stage_cap;	 /* STAGE: shared-memory bytes per group */
 	uint8_t *scratch;	 /* !STAGE: linear slots for non-contiguous dst */
 	uint32_t scratch_stride; /* bytes per slot */
+	/* lane-per-block decoder only (lz4e_decompress_lane.cuh): linear slots
+	 * for compressed blocks whose source is not one contiguous segment */
+	uint8_t *in_scratch;
+	uint32_t in_stride;
 };
 
 
@@ -130,8 +134,26 @@ LZ4E_DEV void lz4e_dgroup_literals(const lz4e_in_view &in, uint8_t *out,
 		lz4e_copy<W>(out, in.bias + ip, len, l);
 		return;
 	}
-	for (uint32_t i = l; i < len; i += W)
-		out[i] = (uint8_t)lz4e_in_rd8(in, ip + i);
+	if (len < 32u) {
+		for (uint32_t i = l; i < len; i += W)
+			out[i] = (uint8_t)lz4e_in_rd8(in, ip + i);
+		return;
+	}
+	/* a long run over several source segments: piece by piece */
+	lz4e_in_view w = in;
+	uint32_t done = 0;
+
+	while (done < len) {
+		const uint32_t p = ip + done;
+
+		lz4e_in_seek(w, p);
+		uint32_t take = w.hi - p;
+
+		if (take > len - done)
+			take = len - done;
+		lz4e_copy<W>(out + done, w.bias + p, take, l);
+		done += take;
+	}
 }
 
 #define LZ4E_P_LIT 1u

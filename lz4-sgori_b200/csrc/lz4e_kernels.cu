@@ -7,6 +7,7 @@
 
 #include "lz4e_compress_body.cuh"
 #include "lz4e_decompress_body.cuh"
+#include "lz4e_decompress_lane.cuh"
 #include "lz4e_kernels.h"
 #include "lz4e_synth.h"
 
@@ -31,6 +32,17 @@ lz4e_decompress_kernel(const lz4e_decompress_args a)
 	const uint32_t slot0 = (blockIdx.x * LZ4E_D_WARPS + warp) * groups;
 
 	lz4e_decompress_warp_impl<GS, STAGE>(a, sm, slot0, threadIdx.x & 31);
+}
+
+/* ---- K4L: lane-per-block decompression, 32 blocks in flight per warp ------ */
+__global__ void __launch_bounds__(LZ4E_D_WARPS * 32)
+lz4e_decompress_lane_kernel(const lz4e_decompress_args a)
+{
+	__shared__ lz4e_lane_smem sm[LZ4E_D_WARPS];
+	const uint32_t warp = threadIdx.x >> 5;
+	const uint32_t slot0 = (blockIdx.x * LZ4E_D_WARPS + warp) * 32u;
+
+	lz4e_decompress_lanes(a, &sm[warp], slot0, threadIdx.x & 31);
 }
 
 /* ---- synthetic contents: one thread writes one linear block --------------- */
@@ -163,9 +175,43 @@ static int launch_decompress_t(const lz4e_decompress_args *a, int sm_count,
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
+static int launch_decompress_lanes(const lz4e_decompress_args *a, int sm_count,
+				   cudaStream_t stream, int grid_limit, int *grid_out)
+{
+	int per_sm = 0;
+
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+		    &per_sm, lz4e_decompress_lane_kernel, LZ4E_D_WARPS * 32, 0) != cudaSuccess ||
+	    per_sm < 1)
+		return -1;
+	long long grid = (long long)per_sm * sm_count;
+	const long long want =
+		((long long)a->nblocks + LZ4E_D_WARPS * 32 - 1) / (LZ4E_D_WARPS * 32);
+
+	if (grid > want)
+		grid = want;
+	if (grid_limit > 0 && grid > grid_limit)
+		grid = grid_limit;
+	if (grid < 1)
+		grid = 1;
+	lz4e_decompress_lane_kernel<<<(unsigned)grid, LZ4E_D_WARPS * 32, 0, stream>>>(*a);
+	if (grid_out)
+		*grid_out = (int)grid;
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
 int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_count)
 {
 	int per_sm = 0;
+
+	if (group == 1) {
+		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+			    &per_sm, lz4e_decompress_lane_kernel, LZ4E_D_WARPS * 32, 0) !=
+			    cudaSuccess ||
+		    per_sm < 1)
+			return -1;
+		return per_sm * sm_count;
+	}
 	size_t smem = stage ? (size_t)LZ4E_D_WARPS * (32 / group) * (stage_cap + LZ4E_D_PAD) : 0;
 	const void *fn;
 
@@ -192,6 +238,8 @@ int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
 			   int sm_count, cudaStream_t stream, int grid_limit,
 			   int *grid_out)
 {
+	if (group == 1)
+		return launch_decompress_lanes(a, sm_count, stream, grid_limit, grid_out);
 	if (stage) {
 		switch (group) {
 		case 8:

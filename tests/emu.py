@@ -67,7 +67,7 @@ def decompress(lib, src_layout, dst_layout, group=8, stage_cap=4096, scratch_str
     n = len(sit)
     rets = np.full(n, -777, dtype=np.int32)
     faults = np.zeros(1, dtype=np.uint32)
-    scratch = np.zeros(max(1, (32 // group) * scratch_stride), dtype=np.uint8)
+    scratch = np.zeros(max(1, (32 // group) * scratch_stride + 64), dtype=np.uint8)
     rc = lib.simt_decompress_batch(_p(sbv), _p(sit), _p(dbv), _p(dit), n, group, stage_cap,
                                    _p(rets), _p(faults), _p(scratch), scratch_stride, seed)
     assert rc == 0

@@ -195,6 +195,7 @@ static void run_warp(const std::function<void(uint32_t)> &body, uint32_t seed)
 
 #include "lz4e_compress_body.cuh"
 #include "lz4e_decompress_body.cuh"
+#include "lz4e_decompress_lane.cuh"
 
 extern "C" {
 
@@ -258,7 +259,7 @@ int simt_decompress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 {
 	lz4e_decompress_args a;
 	uint32_t counter = 0;
-	const uint32_t ngroups = 32 / group;
+	const uint32_t ngroups = 32 / (group ? group : 1);
 	const uint32_t bytes = ngroups * (stage_cap + LZ4E_D_PAD);
 	void *smraw = nullptr;
 
@@ -276,7 +277,24 @@ int simt_decompress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 	a.stage_cap = stage_cap;
 	a.scratch = scratch;
 	a.scratch_stride = scratch_stride;
+	a.in_scratch = nullptr;
+	a.in_stride = 0;
 	uint8_t *sm = (uint8_t *)smraw;
+
+	if (group == 1) {
+		/* lane-per-block decoder: `scratch` holds 32 output slots, the
+		 * input slots are allocated here */
+		lz4e_lane_smem *ls = (lz4e_lane_smem *)calloc(1, sizeof(*ls));
+		uint8_t *ins = (uint8_t *)malloc((size_t)32 * (scratch_stride + 64) + 64);
+
+		a.in_scratch = ins;
+		a.in_stride = scratch_stride + 64;
+		simt::run_warp([&](uint32_t lane) { lz4e_decompress_lanes(a, ls, 0, lane); }, seed);
+		free(ins);
+		free(ls);
+		free(smraw);
+		return 0;
+	}
 
 	simt::run_warp(
 		[&](uint32_t lane) {

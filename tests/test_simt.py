@@ -77,7 +77,7 @@ def test_compress_body_limited_output(simt, ref_lib, out_cap):
         assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
 
 
-@pytest.mark.parametrize("group", [2, 4, 8, 16, 32])
+@pytest.mark.parametrize("group", [1, 2, 4, 8, 16, 32])
 def test_decompress_body_roundtrip(simt, ref_lib, group):
     datas, specs = _cases()
     keep = [i for i, d in enumerate(datas) if len(d) > 0]
@@ -89,6 +89,90 @@ def test_decompress_body_roundtrip(simt, ref_lib, group):
     csrc = sg.Layout(cdst.arena, cdst.bvecs, cdst.first, cdst.iters.copy(), cdst.npages_used)
     csrc.iters["bi_size"] = sizes.astype(np.uint32)
     rets, faults = emu.decompress(simt, csrc, out, group=group, stage_cap=0, scratch_stride=16384)
+    assert faults == 0
+    assert np.array_equal(rets, [len(d) for d in datas])
+    for b, d in enumerate(datas):
+        assert np.array_equal(out.read_block(b), d), b
+
+
+def test_lane_decoder_scattered_source_and_destination(simt, ref_lib):
+    """Lane-per-block decoder (lz4e_decompress_lane.cuh): compressed bytes and output both over
+    odd, non-contiguous segments (gather into a slot, decode, scatter), 40 blocks so lanes
+    take a second block."""
+    rng = np.random.default_rng(11)
+    datas = [common.synth(int(rng.integers(1, 9000)), b & 3, 300 + b) for b in range(40)]
+    src = _host_layout([sg.segs_single(len(d)) for d in datas], datas)
+    cdst, (sizes, _) = common.oracle_compress(ref_lib, src, [sg.segs_single(sg.compress_bound(len(d)))
+                                                             for d in datas])
+    comps = [cdst.read_block(b, sizes[b]) for b in range(len(datas))]
+    csrc = _host_layout([sg.segs_random(len(c), rng) for c in comps], comps)
+    out = _host_layout([sg.segs_random(len(d), rng) for d in datas])
+    rets, faults = emu.decompress(simt, csrc, out, group=1, stage_cap=0, scratch_stride=16384)
+    assert faults == 0
+    assert np.array_equal(rets, [len(d) for d in datas])
+    for b, d in enumerate(datas):
+        assert np.array_equal(out.read_block(b), d), b
+
+
+def test_lane_decoder_malformed_streams(simt, ref_lib):
+    """Mutated, truncated and random streams: return values (incl. the -(offset)-1 codes,
+    lz4e_decompress.c:458-459) and the bytes of accepted streams equal the reference decoder's."""
+    rng = np.random.default_rng(5)
+    base = [common.synth(int(rng.integers(20, 3000)), int(rng.integers(0, 4)), i) for i in range(96)]
+    src = _host_layout([sg.segs_single(len(d)) for d in base], base)
+    cdst, (sizes, _) = common.oracle_compress(ref_lib, src, [sg.segs_single(sg.compress_bound(len(d)))
+                                                             for d in base])
+    comps, caps = [], []
+    for b, d in enumerate(base):
+        c = bytearray(cdst.read_block(b, sizes[b]).tobytes())
+        r = rng.random()
+        if r < 0.3 and len(c) > 2:
+            c = c[:int(rng.integers(1, len(c)))]
+        elif r < 0.6:
+            for _ in range(int(rng.integers(1, 4))):
+                c[int(rng.integers(0, len(c)))] = int(rng.integers(0, 256))
+        elif r < 0.75:
+            c += bytes(rng.integers(0, 256, int(rng.integers(1, 20)), dtype=np.uint8))
+        elif r < 0.85:
+            c = bytearray(rng.integers(0, 256, int(rng.integers(1, 200)), dtype=np.uint8).tobytes())
+        comps.append(np.frombuffer(bytes(c), dtype=np.uint8))
+        caps.append(max(0, len(d) + int(rng.integers(-20, 20))) if rng.random() < 0.4 else len(d))
+    ref_rets, ref_outs = common.oracle_decode_linear(ref_lib, comps, caps)
+    assert (ref_rets < 0).sum() > 10 and (ref_rets >= 0).sum() > 10
+    for seg_mode in (0, 1):
+        mk = (lambda n: sg.segs_random(n, rng)) if seg_mode else \
+            (lambda n: dict(sg.segs_single(max(n, 1)), size=n))
+        csrc = _host_layout([mk(len(c)) for c in comps], comps)
+        out = _host_layout([mk(c) for c in caps])
+        rets, faults = emu.decompress(simt, csrc, out, group=1, stage_cap=0, scratch_stride=16384)
+        assert faults == 0
+        assert np.array_equal(rets, ref_rets)
+        for b in range(len(comps)):
+            if rets[b] > 0:
+                assert np.array_equal(out.read_block(b, rets[b]), ref_outs[b]), b
+
+
+def test_lane_decoder_medium_runs(simt, ref_lib):
+    """Runs of 64..511 bytes on every lane at once (unit lists longer than the shared-memory
+    table: several passes), periods below and above the unit size, literal runs in between."""
+    rng = np.random.default_rng(21)
+    datas = []
+    for b in range(64):
+        parts = []
+        while sum(len(p) for p in parts) < 3000:
+            period = int(rng.choice([1, 2, 3, 5, 7, 8, 9, 12, 16, 31, 40, 100]))
+            pat = rng.integers(0, 256, period, dtype=np.uint8)
+            n = int(rng.integers(64, 520))
+            parts.append(np.tile(pat, n // period + 1)[:n])
+            parts.append(rng.integers(0, 256, int(rng.integers(1, 90)), dtype=np.uint8))
+        datas.append(np.concatenate(parts))
+    src = _host_layout([sg.segs_single(len(d)) for d in datas], datas)
+    cdst, (sizes, _) = common.oracle_compress(ref_lib, src, [sg.segs_single(sg.compress_bound(len(d)))
+                                                             for d in datas])
+    csrc = sg.Layout(cdst.arena, cdst.bvecs, cdst.first, cdst.iters.copy(), cdst.npages_used)
+    csrc.iters["bi_size"] = sizes.astype(np.uint32)
+    out = _host_layout([sg.segs_single(len(d)) for d in datas])
+    rets, faults = emu.decompress(simt, csrc, out, group=1, stage_cap=0, scratch_stride=16384)
     assert faults == 0
     assert np.array_equal(rets, [len(d) for d in datas])
     for b, d in enumerate(datas):
