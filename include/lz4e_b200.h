@@ -107,6 +107,12 @@ int lz4e_b200_sync(lz4e_b200_ctx *ctx, void *stream);
 				     * is reserved for the lane-per-block
 				     * decoder) */
 
+/* largest block of one *_dev compress call: 16 MiB.  Up to 64 KiB the hash
+ * table holds 16-bit positions; above, 32-bit ones (same number of entries as
+ * lz4e_compress.c:48-57) and the block is read from a gather slot in global
+ * memory (bios of 128 KiB ... 4 MiB, multi-page bvecs) */
+#define LZ4E_B200_MAX_BLOCK (16u << 20)
+
 /*
  * LZ4E_compress_default for `nblocks` independent blocks.
  *  src_bvecs/src_iters   source tables (device memory)

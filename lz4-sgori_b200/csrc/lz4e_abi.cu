@@ -503,9 +503,9 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 		return LZ4E_B200_ENODEV;
 	if (nblocks == 0)
 		return LZ4E_B200_OK;
-	if (max_in_bytes > 65536u) {
-		set_err(ctx, "blocks above 65536 bytes (%u) are not supported by the "
-			     "compressor yet (16-bit table positions)", max_in_bytes);
+	if (max_in_bytes > LZ4E_B200_MAX_BLOCK) {
+		set_err(ctx, "blocks above %u bytes (%u) are not supported by the "
+			     "compressor", (unsigned)LZ4E_B200_MAX_BLOCK, max_in_bytes);
 		return LZ4E_B200_EINVAL;
 	}
 	cudaSetDevice(ctx->device);
@@ -520,6 +520,8 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 	a.faults = ctx->d_ctl + CTL_FAULTS;
 	a.nblocks = nblocks;
 	a.table_bytes = (flags & LZ4E_B200_DEV_NO_BYU16) ? 8192u : 16384u;
+	if (max_in_bytes > 65536u) /* 32-bit positions: 4096 entries of 4 bytes */
+		a.table_bytes = 16384u;
 	a.in_cap = (max_in_bytes + 15u) & ~15u;
 	if (a.in_cap < 16)
 		a.in_cap = 16;
@@ -540,7 +542,7 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 		/* large blocks: input in a global slot read through L1 instead of
 		 * shared memory (64 KiB blocks: 3 -> 16 resident warps per SM) */
 		const int direct = (flags & LZ4E_B200_DEV_DST_LINEAR) ? 1 : 0;
-		const int gin = (int)max_in_bytes > ctx->gin_min;
+		const int gin = (int)max_in_bytes > ctx->gin_min || max_in_bytes > 65536u;
 		int grid = 0;
 		size_t smem = 0;
 
@@ -553,7 +555,15 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 			return LZ4E_B200_EIO;
 		}
 		if (gin) {
+			/* input slots of one launch stay below 4 GiB */
+			const size_t budget = (size_t)4 << 30;
+
 			a.in_stride = ((a.in_cap + 63u) & ~255u) + 256u;
+			if ((size_t)grid * a.in_stride > budget) {
+				grid = (int)(budget / a.in_stride);
+				if (grid < 1)
+					grid = 1;
+			}
 			a.in_scratch = compress_slots(ctx, s, (size_t)grid * a.in_stride + 256);
 			if (!a.in_scratch) {
 				set_err(ctx, "compress input slots (%zu bytes): out of device memory",

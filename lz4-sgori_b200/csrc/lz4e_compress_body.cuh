@@ -170,7 +170,7 @@ LZ4E_DEV void lz4e_put_run(uint8_t *p, uint32_t count, uint32_t last,
  * Returns the reference's return value; src_end/dst_end receive the iterator
  * end state.
  */
-template <int TT, bool DIRECT, bool GIN>
+template <int TT, bool DIRECT, bool GIN, typename TABT>
 LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				      const struct lz4e_b200_dev_iter &di,
 				      const uint8_t *d, uint32_t n, uint8_t *sm,
@@ -178,7 +178,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				      uint32_t &src_end, uint32_t &dst_end)
 {
 	const uint32_t cap = di.bi_size;
-	uint16_t *tab = reinterpret_cast<uint16_t *>(sm);
+	TABT *tab = reinterpret_cast<TABT *>(sm);
 	int32_t ret = 0;
 
 	if (GIN)
@@ -223,10 +223,11 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 		}
 
 		if (n >= 13) {
-			/* zero the table: (1 << hashLog) 16-bit entries */
-			const uint32_t tbytes = TT == LZ4E_TT_U16   ? 16384u
-						: TT == LZ4E_TT_U32 ? 8192u
-								    : 4096u;
+			/* zero the table: (1 << hashLog) entries of TABT (16-bit
+			 * positions up to 64 KiB, 32-bit ones above) */
+			const uint32_t tbytes = (TT == LZ4E_TT_U16   ? 8192u
+						 : TT == LZ4E_TT_U32 ? 4096u
+								     : 2048u) * (uint32_t)sizeof(TABT);
 			const lz4e_u128 z = { 0, 0, 0, 0 };
 
 			if (tbytes > a.table_bytes) {
@@ -301,7 +302,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					}
 					/* commit all 32 visits, keep searching */
 					if ((peers >> lane) >> 1 == 0)
-						tab[h] = (uint16_t)pos;
+						tab[h] = (TABT)pos;
 					lz4e_syncwarp(LZ4E_FULL);
 					kbase += 32;
 					continue;
@@ -312,7 +313,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 
 				if ((int)lane <= f &&
 				    (peers & ((2u << f) - 1u) & ~((2u << lane) - 1u)) == 0)
-					tab[h] = (uint16_t)pos;
+					tab[h] = (TABT)pos;
 
 				ip = lz4e_shfl(LZ4E_FULL, pos, f);
 				mp = lz4e_shfl(LZ4E_FULL, m, f);
@@ -376,8 +377,8 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					/* the lane that guessed the length holds the hashes of
 					 * :461-464 and :467-470 for the new anchor q == na */
 					if (lane == ml && !last) {
-						tab[qh2] = (uint16_t)(q - 2u);
-						tab[qh] = (uint16_t)q;
+						tab[qh2] = (TABT)(q - 2u);
+						tab[qh] = (TABT)q;
 					}
 					anchor = ip = na;
 					p0 = na + 1u; /* if no match follows: search from ip + 1 */
@@ -577,8 +578,8 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 
 					mp = lz4e_shfl(LZ4E_FULL, q_m, (int)ml);
 					if (lane == ml) {
-						tab[q_h2] = (uint16_t)(anchor - 2u);
-						tab[q_h] = (uint16_t)anchor;
+						tab[q_h2] = (TABT)(anchor - 2u);
+						tab[q_h] = (TABT)anchor;
 					}
 					ip = anchor;
 					have = (okm >> ml) & 1u; /* else: search from ip + 1 */
@@ -647,7 +648,7 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 
 	if (n > LZ4E_K_MAX_INPUT) /* lz4e_compress.c:245-248 */
 		goto done;
-	if (n > a.in_cap || n > 65536u) {
+	if (n > a.in_cap || (n > 65536u && !GIN)) {
 		if (lane == 0)
 			lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
 		goto done;
@@ -702,18 +703,32 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 		lz4e_syncwarp(LZ4E_FULL); /* gathered bytes visible to all lanes */
 	}
 
+	if (GIN && n > 65536u) {
+		/* positions no longer fit 16 bits: same table sizes in entries
+		 * (lz4e_compress.c:48-57), 32-bit linear positions.  byU16 cannot
+		 * occur here: it needs <= 16 bvecs of <= 4096 bytes (:200-202) */
+		if (tt == LZ4E_TT_U32)
+			ret = lz4e_compress_encode<LZ4E_TT_U32, DIRECT, GIN, uint32_t>(
+				a, di, d, n, sm, out_area, lane, src_end, dst_end);
+		else if (tt == LZ4E_TT_U64)
+			ret = lz4e_compress_encode<LZ4E_TT_U64, DIRECT, GIN, uint32_t>(
+				a, di, d, n, sm, out_area, lane, src_end, dst_end);
+		else if (lane == 0)
+			lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
+		goto done;
+	}
 	switch (tt) {
 	case LZ4E_TT_U16:
-		ret = lz4e_compress_encode<LZ4E_TT_U16, DIRECT, GIN>(a, di, d, n, sm, out_area, lane,
-							src_end, dst_end);
+		ret = lz4e_compress_encode<LZ4E_TT_U16, DIRECT, GIN, uint16_t>(
+			a, di, d, n, sm, out_area, lane, src_end, dst_end);
 		break;
 	case LZ4E_TT_U32:
-		ret = lz4e_compress_encode<LZ4E_TT_U32, DIRECT, GIN>(a, di, d, n, sm, out_area, lane,
-							src_end, dst_end);
+		ret = lz4e_compress_encode<LZ4E_TT_U32, DIRECT, GIN, uint16_t>(
+			a, di, d, n, sm, out_area, lane, src_end, dst_end);
 		break;
 	default:
-		ret = lz4e_compress_encode<LZ4E_TT_U64, DIRECT, GIN>(a, di, d, n, sm, out_area, lane,
-							src_end, dst_end);
+		ret = lz4e_compress_encode<LZ4E_TT_U64, DIRECT, GIN, uint16_t>(
+			a, di, d, n, sm, out_area, lane, src_end, dst_end);
 		break;
 	}
 

@@ -191,3 +191,25 @@ def test_decompress_stress_overlap_and_literals(ctx, ref_lib):
         for k, i in enumerate(sel):
             assert r2[k] == len(datas[i])
             assert np.array_equal(out.read_block(k), datas[i])
+
+
+def test_blocks_above_64k(ctx, ref_lib):
+    """bios of 68 KiB ... 1 MiB (multi-page bvecs, more than 16 bvecs): 32-bit
+    table positions, byte-identical to the reference, round trip through the SG decoder."""
+    sizes = [70000, 98304, 131072, 150000, 262144, 1048576]
+    datas = [common.lcg_text(sizes[0]), common.synth(sizes[1], 3, 5), common.synth(sizes[2], 0, 9),
+             np.zeros(sizes[3], np.uint8), common.synth(sizes[4], 2, 11),
+             np.concatenate([common.synth(65536, b & 3, 70 + b) for b in range(16)])]
+    specs = [sg.segs_single(sizes[0]), sg.segs_odd(sizes[1], 24, 1), sg.segs_pages(sizes[2]),
+             sg.segs_single(sizes[3]), sg.segs_odd(sizes[4], 64, 2), sg.segs_pages(sizes[5])]
+    dspecs = [sg.segs_odd(sg.compress_bound(n), 9, 3 + i) for i, n in enumerate(sizes)]
+    src, dst, rets = _check_compress(ctx, ref_lib, datas, specs, dspecs)
+    out = common.build_layout(_arena(ctx), [sg.segs_odd(n, 7, i) for i, n in enumerate(sizes)])
+    r2 = common.gpu_decompress(ctx, dst, rets, out)
+    assert np.array_equal(r2, np.array(sizes, np.int32))
+    for b in range(len(sizes)):
+        assert np.array_equal(out.read_block(b), datas[b])
+    # a mixed batch: small blocks next to large ones in one launch
+    datas2 = [common.synth(4096, 3, 1), datas[1], common.synth(65536, 0, 2), datas[0]]
+    specs2 = [sg.segs_single(4096), specs[1], sg.segs_odd(65536, 16, 4), specs[0]]
+    _check_compress(ctx, ref_lib, datas2, specs2)

@@ -177,3 +177,23 @@ def test_lane_decoder_medium_runs(simt, ref_lib):
     assert np.array_equal(rets, [len(d) for d in datas])
     for b, d in enumerate(datas):
         assert np.array_equal(out.read_block(b), d), b
+
+
+def test_compress_body_blocks_above_64k(simt, ref_lib):
+    """SURVEY row f4: above 64 KiB the table holds 32-bit positions (GIN kernels only);
+    byU32 by construction (a bvec > 4096 bytes or more than 16 bvecs)."""
+    datas = [common.lcg_text(70000), common.synth(98304, 3, 5), np.zeros(150000, np.uint8),
+             common.synth(131072, 0, 9)]
+    specs = [sg.segs_single(70000), sg.segs_odd(98304, 24, 1), sg.segs_single(150000),
+             sg.segs_odd(131072, 32, 2)]
+    src = _host_layout(specs, datas)
+    dspecs = [sg.segs_single(sg.compress_bound(len(d))) for d in datas]
+    dst = _host_layout(dspecs)
+    dst.arena.mem[:] = 0xEE
+    rets, ends, faults = emu.compress(simt, src, dst, in_cap=150016, out_cap=2048, gin=True)
+    ref_dst, (ref_rets, _, so, do) = common.oracle_compress(ref_lib, src, dspecs, want_iters=True)
+    assert faults == 0
+    assert np.array_equal(rets, ref_rets)
+    for b in range(len(datas)):
+        assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
+        assert int(ends[b]["src_pos"]) == len(datas[b]) - int(so[b]["bi_size"]), b
