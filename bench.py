@@ -326,7 +326,7 @@ def run_ours(args):
             "kernel_ms": {"compress": round(c_ms, 4), "decompress": round(d_ms, 4)},
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(ach, 2), "peak": peak,
                          "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak, 5),
-                         "traffic": None,
+                         "traffic": profile_traffic(dom),
                          "algorithmic_bytes_per_launch": int(alg)},
             "roofline_other": {
                 "kernel": "lz4e_decompress_kernel" if dom.startswith("lz4e_c") else "lz4e_compress_kernel",
@@ -342,6 +342,8 @@ def run_ours(args):
             result["extra"] = {"cfg3_64k": run_cfg3(torch, pkg, ctx, stream, args)}
         except Exception as e:  # the headline line must still print
             result["extra"] = {"cfg3_64k": {"error": repr(e)}}
+    if rank == 0 and world == 1 and not args.no_extra:
+        result["extra"]["cfg5_replay"] = run_replay()
     if rank == 0 and world == 1 and not args.no_e2e:
         result["e2e"] = run_e2e(torch, pkg, ctx, args)
     elif rank == 0:
@@ -354,6 +356,38 @@ def run_ours(args):
     if rank == 0:
         print(json.dumps(result))
     ctx.close()
+
+
+def profile_traffic(kernel):
+    """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch of `kernel` at
+    this bench's size, from the committed `ncu --set full` capture (profiles/traffic.json,
+    written by tools/ncu_traffic.py); None when no capture of that kernel is committed."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        e = t.get(kernel)
+        if e and int(e.get("blocks", 0)) == BLOCKS_PER_GPU:
+            return int(e["dram_bytes_per_launch"])
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
+def run_replay():
+    """BASELINE.json configs[4]: the C replay harness of the chunk layer / request path
+    (tools/replay/lz4e_replay.c), QD256 random 4-128 KiB writes/reads on this GPU."""
+    import subprocess
+    exe = os.path.join(ROOT, "tools", "replay", "lz4e_replay")
+    try:
+        if not os.path.exists(exe):
+            subprocess.run(["make", "-C", os.path.dirname(exe)], check=True, capture_output=True)
+        out = subprocess.run([exe, "--arena-bios", "--batches", "48"], capture_output=True,
+                             text=True, timeout=120)
+        if out.returncode != 0:
+            return {"error": "rc=%d %s" % (out.returncode, out.stderr[-300:])}
+        return json.loads(out.stdout.strip().splitlines()[-1])
+    except Exception as e:
+        return {"error": repr(e)}
 
 
 def run_cfg3(torch, pkg, ctx, stream, args):

@@ -17,9 +17,10 @@
 
 #define POOL_CLASSES 513 /* free lists for runs of 1..512 pages */
 
-struct run_hdr {
-	struct run_hdr *next;
-};
+/* free runs are linked OUT of band (page index -> next page index + 1): pool
+ * pages are arena pages, and a batch brings the touched byte range of an arena
+ * back from the device in one bulk copy, which may overwrite free pages that
+ * lie inside that range */
 
 static pthread_mutex_t p_mu = PTHREAD_MUTEX_INITIALIZER;
 static struct {
@@ -27,7 +28,8 @@ static struct {
 	lz4e_b200_arena *arena;
 	uint8_t *base;
 	size_t npages, bump;
-	struct run_hdr *freel[POOL_CLASSES];
+	size_t freel[POOL_CLASSES]; /* first free run of that many pages, + 1 */
+	size_t *next;		    /* per page index */
 	size_t live;
 	int ready;
 } pool;
@@ -50,6 +52,11 @@ static int pool_init_locked(lz4e_b200_ctx *ctx, size_t pool_pages)
 	}
 	if (lz4e_b200_arena_create(ctx, pool_pages, &pool.arena) != LZ4E_B200_OK)
 		return -ENOMEM;
+	pool.next = calloc(pool_pages, sizeof(*pool.next));
+	if (!pool.next) {
+		lz4e_b200_arena_destroy(pool.arena);
+		return -ENOMEM;
+	}
 	pool.ctx = ctx;
 	pool.base = (uint8_t *)lz4e_b200_arena_pages(pool.arena);
 	pool.npages = pool_pages;
@@ -75,6 +82,7 @@ void lz4e_chunk_teardown(void)
 	pthread_mutex_lock(&p_mu);
 	if (pool.ready && pool.live == 0) {
 		lz4e_b200_arena_destroy(pool.arena);
+		free(pool.next);
 		memset(&pool, 0, sizeof(pool));
 	}
 	pthread_mutex_unlock(&p_mu);
@@ -92,8 +100,10 @@ static void *pool_alloc(size_t bytes, int *from_pool)
 	pthread_mutex_lock(&p_mu);
 	if (pool_init_locked(NULL, 0) == 0 && pages < POOL_CLASSES) {
 		if (pool.freel[pages]) {
-			p = pool.freel[pages];
-			pool.freel[pages] = pool.freel[pages]->next;
+			const size_t idx = pool.freel[pages] - 1;
+
+			p = pool.base + (idx << PAGE_SHIFT);
+			pool.freel[pages] = pool.next[idx];
 		} else if (pool.bump + pages <= pool.npages) {
 			p = pool.base + (pool.bump << PAGE_SHIFT);
 			pool.bump += pages;
@@ -123,16 +133,22 @@ static void pool_free(void *p, size_t bytes)
 	pthread_mutex_lock(&p_mu);
 	if (pool.ready && (uint8_t *)p >= pool.base &&
 	    (uint8_t *)p < pool.base + (pool.npages << PAGE_SHIFT)) {
-		struct run_hdr *h = (struct run_hdr *)p;
+		const size_t idx = (size_t)((uint8_t *)p - pool.base) >> PAGE_SHIFT;
 
-		h->next = pool.freel[pages];
-		pool.freel[pages] = h;
+		pool.next[idx] = pool.freel[pages];
+		pool.freel[pages] = idx + 1;
 		pool.live--;
 		pthread_mutex_unlock(&p_mu);
 		return;
 	}
 	pthread_mutex_unlock(&p_mu);
 	free(p);
+}
+
+static int in_pool(const void *p)
+{
+	return pool.ready && (const uint8_t *)p >= pool.base &&
+	       (const uint8_t *)p < pool.base + (pool.npages << PAGE_SHIFT);
 }
 
 static lz4e_b200_ctx *chunk_ctx(void)
@@ -197,8 +213,10 @@ struct lz4e_chunk *lz4e_chunk_alloc(int src_size)
 	if (!chunk->dst_buf.data)
 		goto free_chunk;
 	/* the GPU keeps its hash table on chip; wrkmem stays part of the chunk
-	 * because LZ4E_compress_default's signature carries it */
-	chunk->wrkmem = calloc(1, LZ4E_MEM_COMPRESS);
+	 * because LZ4E_compress_default's signature carries it
+	 * (the callee clears it, lz4e_compress.c:548; not touched here, so the
+	 * allocation costs no page faults) */
+	chunk->wrkmem = malloc(LZ4E_MEM_COMPRESS);
 	if (!chunk->wrkmem)
 		goto free_chunk;
 	return chunk;
@@ -318,10 +336,30 @@ static int chunk_batch(struct lz4e_chunk **chunks, size_t n, int *status, int op
 			break;
 		}
 	}
-	if (op == OP_DECOMPRESS)
-		rc = lz4e_b200_decompress_batch(ctx, w.reqs, n, 0);
-	else
-		rc = lz4e_b200_compress_batch(ctx, w.reqs, n, LZ4E_B200_F_KEEP_ITERS);
+	{
+		/* The library brings an arena's touched range back in one bulk
+		 * copy (lz4e_b200.h).  When pool buffers OUTSIDE this batch are
+		 * live (another chunk filled by lz4e_buf_copy_from_bio, say), that
+		 * copy must not replace them with the device mirror's stale bytes:
+		 * ask for the range to be uploaded first.  A batch that owns every
+		 * live pool buffer (the request path below) skips that. */
+		unsigned int flags = 0;
+		size_t mine = 0, live;
+
+		for (i = 0; i < n; i++)
+			mine += (size_t)in_pool(chunks[i]->src_buf.data) +
+				(size_t)in_pool(chunks[i]->dst_buf.data);
+		pthread_mutex_lock(&p_mu);
+		live = pool.live;
+		pthread_mutex_unlock(&p_mu);
+		if (live > mine)
+			flags |= LZ4E_B200_F_DST_PRESERVE;
+		if (op == OP_DECOMPRESS)
+			rc = lz4e_b200_decompress_batch(ctx, w.reqs, n, flags);
+		else
+			rc = lz4e_b200_compress_batch(ctx, w.reqs, n,
+						      flags | LZ4E_B200_F_KEEP_ITERS);
+	}
 	for (i = 0; i < n; i++) {
 		struct lz4e_chunk *c = chunks[i];
 		const int ret = w.reqs[i].ret;

@@ -604,6 +604,10 @@ static int run_batch(lz4e_b200_ctx *ctx, struct lz4e_b200_req *reqs, size_t n,
 	for (i = 0; i < n; i++)
 		total += (uint64_t)reqs[i].src_iter->bi_size + reqs[i].dst_iter->bi_size;
 	target = chunk_target_bytes(total);
+	/* few blocks: one kernel (each block is one warp's serial work, so two
+	 * half-empty kernels one after the other only double the latency) */
+	if (n < 4096 && !getenv("LZ4E_B200_CHUNK_MB"))
+		target = (size_t)-1;
 	if (total > target) {
 		/*
 		 * More than one chunk: uploads of later chunks and downloads of

@@ -19,6 +19,9 @@
 #define _GNU_SOURCE
 #include <dlfcn.h>
 #include <errno.h>
+#include <execinfo.h>
+#include <signal.h>
+#include <unistd.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -90,6 +93,17 @@ static void bio_fill_pages(struct slot *s, unsigned int bytes, uint64_t pos)
 	s->bio.bi_iter.bi_size = bytes;
 	s->bio.bi_iter.bi_idx = 0;
 	s->bio.bi_iter.bi_bvec_done = 0;
+}
+
+/* a crash inside the library should say where */
+static void on_fatal(int sig)
+{
+	void *bt[48];
+	const int n = backtrace(bt, 48);
+
+	fprintf(stderr, "lz4e_replay: signal %d\n", sig);
+	backtrace_symbols_fd(bt, n, 2);
+	_exit(128 + sig);
 }
 
 typedef int (*ref_compress_fn)(const struct bio_vec *, struct bio_vec *, struct bvec_iter *,
@@ -165,6 +179,8 @@ int main(int argc, char **argv)
 	void *ref_wrk = NULL;
 	struct lz4e_stats ws, rs;
 
+	signal(SIGBUS, on_fatal);
+	signal(SIGSEGV, on_fatal);
 	if (parse(argc, argv, &o)) {
 		usage();
 		return 2;
