@@ -559,12 +559,12 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 			const size_t budget = (size_t)4 << 30;
 
 			a.in_stride = ((a.in_cap + 63u) & ~255u) + 256u;
-			if ((size_t)grid * a.in_stride > budget) {
-				grid = (int)(budget / a.in_stride);
+			if ((size_t)grid * a.warps * a.in_stride > budget) {
+				grid = (int)(budget / a.in_stride / a.warps);
 				if (grid < 1)
 					grid = 1;
 			}
-			a.in_scratch = compress_slots(ctx, s, (size_t)grid * a.in_stride + 256);
+			a.in_scratch = compress_slots(ctx, s, (size_t)grid * a.warps * a.in_stride + 256);
 			if (!a.in_scratch) {
 				set_err(ctx, "compress input slots (%zu bytes): out of device memory",
 					(size_t)grid * a.in_stride);

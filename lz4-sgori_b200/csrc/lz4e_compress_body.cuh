@@ -68,6 +68,10 @@ struct lz4e_compress_args {
 	 * limit the number of resident warps */
 	uint8_t *in_scratch;
 	uint32_t in_stride; /* bytes per slot, >= in_cap + 64 */
+	/* CTA shape, set by lz4e_compress_plan(): warps per CTA and the shared
+	 * memory stride from one warp's area to the next */
+	uint32_t warps;
+	uint32_t warp_smem;
 };
 
 /* shared memory needed by one warp (in_cap = 0 for the GIN kernels) */

@@ -13,12 +13,17 @@
 
 extern __shared__ __align__(16) uint8_t lz4e_smem[];
 
-/* ---- K2: compression, one warp (= one CTA) per block in flight ----------- */
+/* ---- K2: compression, one warp per block in flight; a.warps warps per CTA,
+ * each with its own a.warp_smem bytes of shared memory ---------------------- */
+#define LZ4E_C_MAX_WARPS 12
 template <bool DIRECT, bool GIN>
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(LZ4E_C_MAX_WARPS * 32)
 lz4e_compress_kernel(const lz4e_compress_args a)
 {
-	lz4e_compress_warp<DIRECT, GIN>(a, lz4e_smem, threadIdx.x, blockIdx.x);
+	const uint32_t w = threadIdx.x >> 5;
+
+	lz4e_compress_warp<DIRECT, GIN>(a, lz4e_smem + (size_t)w * a.warp_smem, threadIdx.x & 31,
+					blockIdx.x * a.warps + w);
 }
 
 /* ---- K4: decompression, LZ4E_D_WARPS warps per CTA, 32/GS blocks per warp */
@@ -103,13 +108,16 @@ static lz4e_compress_fn compress_fn(int direct, int gin)
  * which shares the SM's 256 KB with shared memory: fewer, better cached warps
  * can beat more warps).
  */
-int lz4e_compress_plan(const lz4e_compress_args *a, int direct, int gin, int sm_count,
+int lz4e_compress_plan(lz4e_compress_args *a, int direct, int gin, int sm_count,
 		       int max_per_sm, int *grid_out, size_t *smem_out)
 {
 	size_t smem = lz4e_compress_smem_bytes(a->table_bytes, gin ? 0u : a->in_cap, a->out_cap);
 	int per_sm = 0;
 	lz4e_compress_fn fn = compress_fn(direct, gin);
 
+	smem = (smem + 15) & ~(size_t)15;
+	a->warps = 1;
+	a->warp_smem = (uint32_t)smem;
 	if (max_per_sm > 0) {
 		/* ask for enough shared memory that only max_per_sm CTAs fit */
 		const size_t want = ((size_t)227 * 1024 / (size_t)max_per_sm - 1024) & ~(size_t)127;
@@ -123,6 +131,33 @@ int lz4e_compress_plan(const lz4e_compress_args *a, int direct, int gin, int sm_
 		    cudaSuccess ||
 	    per_sm < 1)
 		return -1;
+	if (max_per_sm <= 0) {
+		/* every CTA pays 1 KB of reserved shared memory: ONE CTA of W warps
+		 * per SM can hold more warps than W one-warp CTAs (4 KiB blocks
+		 * written in place: 11 instead of 10) */
+		const size_t cta_max = (size_t)227 * 1024;
+		int w = (int)(cta_max / a->warp_smem);
+
+		if (w > LZ4E_C_MAX_WARPS)
+			w = LZ4E_C_MAX_WARPS;
+		if (w > per_sm && (long long)a->nblocks >= (long long)w * sm_count) {
+			int one = 0;
+			const size_t big = (size_t)w * a->warp_smem;
+
+			if (lz4e_set_smem((const void *)fn, big) == 0 &&
+			    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&one, fn, w * 32, big) ==
+				    cudaSuccess &&
+			    one >= 1) {
+				a->warps = (uint32_t)w;
+				*grid_out = sm_count * one;
+				*smem_out = big;
+				return 0;
+			}
+			(void)cudaGetLastError();
+			if (lz4e_set_smem((const void *)fn, smem))
+				return -1;
+		}
+	}
 	long long grid = (long long)per_sm * sm_count;
 
 	if (grid > (long long)a->nblocks)
@@ -139,7 +174,7 @@ int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int gin, int g
 {
 	lz4e_compress_fn fn = compress_fn(direct, gin);
 
-	fn<<<(unsigned)grid, 32, smem, stream>>>(*a);
+	fn<<<(unsigned)grid, 32u * a->warps, smem, stream>>>(*a);
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 

@@ -12,7 +12,7 @@
 struct lz4e_compress_args;
 struct lz4e_decompress_args;
 
-int lz4e_compress_plan(const lz4e_compress_args *a, int direct, int gin, int sm_count,
+int lz4e_compress_plan(lz4e_compress_args *a, int direct, int gin, int sm_count,
 		       int max_per_sm, int *grid_out, size_t *smem_out);
 int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int gin, int grid,
 			 size_t smem, cudaStream_t stream);
