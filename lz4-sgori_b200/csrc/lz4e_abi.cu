@@ -593,13 +593,20 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 	cudaStream_t s;
 	int stage, grid_limit = 0;
 	/*
-	 * lanes per block: 8 for the 4 KiB chunk size, 16 for large blocks
-	 * (measured on B200: 64 KiB blocks 106 -> 130 GB/s; 4 KiB 290 vs 225).
+	 * lanes per block: 8 for the 4 KiB chunk size, 16 for large blocks in
+	 * small batches (measured on B200: 64 KiB blocks 106 -> 130 GB/s; 4 KiB
+	 * 290 vs 225).
 	 * Small blocks in batches large enough to give every resident lane a
 	 * block of its own go to the lane-per-block decoder ("1"; 4 KiB mixed
 	 * 290 -> 325 GB/s at 262144 blocks, but 140 vs 232 GB/s at 65536).
 	 */
 	int group = (ctx && ctx->dgroup) ? ctx->dgroup : (max_out_bytes > 8192u ? 16 : 8);
+
+	/* large blocks: 8 lanes per block once the batch fills every resident
+	 * group of 8 (64 KiB over 16 segments, 32768 blocks: 150 -> 161 GB/s) */
+	if (ctx && !ctx->dgroup && max_out_bytes > 8192u &&
+	    nblocks >= (uint32_t)ctx->sm_count * 9u * LZ4E_D_WARPS * 4u)
+		group = 8;
 
 	if (ctx && !ctx->dgroup && max_out_bytes <= 8192u &&
 	    nblocks >= (uint32_t)ctx->sm_count * 24u * 32u)

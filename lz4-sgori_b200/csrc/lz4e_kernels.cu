@@ -15,7 +15,7 @@ extern __shared__ __align__(16) uint8_t lz4e_smem[];
 
 /* ---- K2: compression, one warp per block in flight; a.warps warps per CTA,
  * each with its own a.warp_smem bytes of shared memory ---------------------- */
-#define LZ4E_C_MAX_WARPS 12
+#define LZ4E_C_MAX_WARPS 24
 template <bool DIRECT, bool GIN>
 __global__ void __launch_bounds__(LZ4E_C_MAX_WARPS * 32)
 lz4e_compress_kernel(const lz4e_compress_args a)
