@@ -50,6 +50,8 @@ struct lz4e_b200_ctx {
 	std::vector<cslot> cscratch;
 	int gin_min;	 /* blocks above this many bytes use the GIN compress kernels */
 	int gin_per_sm;	 /* resident warps per SM for them (0: as many as fit) */
+	int gin_small;	 /* batches of up to this many waves of resident shared-memory
+			  * warps keep their input in shared memory (0: never) */
 	std::mutex mu;
 	std::vector<lz4e_b200_arena *> arenas;
 	char err[256];
@@ -139,6 +141,9 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 		ctx->dstage = atoi(e) ? 1 : 0;
 	ctx->gin_min = 12288;
 	ctx->gin_per_sm = 0;
+	ctx->gin_small = 2;
+	if (const char *e = getenv("LZ4E_B200_GIN_SMALL"))
+		ctx->gin_small = atoi(e);
 	if (const char *e = getenv("LZ4E_B200_GIN_MIN"))
 		ctx->gin_min = atoi(e);
 	if (const char *e = getenv("LZ4E_B200_GIN_PER_SM"))
@@ -542,7 +547,23 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 		/* large blocks: input in a global slot read through L1 instead of
 		 * shared memory (64 KiB blocks: 3 -> 16 resident warps per SM) */
 		const int direct = (flags & LZ4E_B200_DEV_DST_LINEAR) ? 1 : 0;
-		const int gin = (int)max_in_bytes > ctx->gin_min || max_in_bytes > 65536u;
+		int gin = (int)max_in_bytes > ctx->gin_min;
+
+		/* a batch small enough to be resident all at once with its input
+		 * in SHARED memory runs there: with few warps per SM occupancy is
+		 * no concern and shared-memory loads beat loads through L1/L2 */
+		{
+			const size_t per_warp =
+				lz4e_compress_smem_bytes(a.table_bytes, a.in_cap, a.out_cap);
+			const size_t cta_max = (size_t)227 * 1024 - 1024;
+
+			if (per_warp > cta_max)
+				gin = 1;
+			else if (gin && ctx->gin_small > 0 &&
+				 (size_t)nblocks <= (size_t)ctx->sm_count * (cta_max / per_warp) *
+							    (size_t)ctx->gin_small)
+				gin = 0;
+		}
 		int grid = 0;
 		size_t smem = 0;
 

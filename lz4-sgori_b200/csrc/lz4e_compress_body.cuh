@@ -652,7 +652,7 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 
 	if (n > LZ4E_K_MAX_INPUT) /* lz4e_compress.c:245-248 */
 		goto done;
-	if (n > a.in_cap || (n > 65536u && !GIN)) {
+	if (n > a.in_cap) {
 		if (lane == 0)
 			lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
 		goto done;
@@ -707,9 +707,10 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 		lz4e_syncwarp(LZ4E_FULL); /* gathered bytes visible to all lanes */
 	}
 
-	if (GIN && n > 65536u) {
+	if (n > 65536u) {
 		/* positions no longer fit 16 bits: same table sizes in entries
-		 * (lz4e_compress.c:48-57), 32-bit linear positions.  byU16 cannot
+		 * (lz4e_compress.c:48-57), 32-bit linear positions (the launch
+		 * reserved 16 KiB of table for them).  byU16 cannot
 		 * occur here: it needs <= 16 bvecs of <= 4096 bytes (:200-202) */
 		if (tt == LZ4E_TT_U32)
 			ret = lz4e_compress_encode<LZ4E_TT_U32, DIRECT, GIN, uint32_t>(

@@ -179,8 +179,10 @@ def test_lane_decoder_medium_runs(simt, ref_lib):
         assert np.array_equal(out.read_block(b), d), b
 
 
-def test_compress_body_blocks_above_64k(simt, ref_lib):
-    """SURVEY row f4: above 64 KiB the table holds 32-bit positions (GIN kernels only);
+@pytest.mark.parametrize("gin", [True, False])
+def test_compress_body_blocks_above_64k(simt, ref_lib, gin):
+    """above 64 KiB the table holds 32-bit positions (input in a global slot, or
+    in shared memory for batches small enough to be resident at once);
     byU32 by construction (a bvec > 4096 bytes or more than 16 bvecs)."""
     datas = [common.lcg_text(70000), common.synth(98304, 3, 5), np.zeros(150000, np.uint8),
              common.synth(131072, 0, 9)]
@@ -190,7 +192,7 @@ def test_compress_body_blocks_above_64k(simt, ref_lib):
     dspecs = [sg.segs_single(sg.compress_bound(len(d))) for d in datas]
     dst = _host_layout(dspecs)
     dst.arena.mem[:] = 0xEE
-    rets, ends, faults = emu.compress(simt, src, dst, in_cap=150016, out_cap=2048, gin=True)
+    rets, ends, faults = emu.compress(simt, src, dst, in_cap=150016, out_cap=2048, gin=gin)
     ref_dst, (ref_rets, _, so, do) = common.oracle_compress(ref_lib, src, dspecs, want_iters=True)
     assert faults == 0
     assert np.array_equal(rets, ref_rets)
