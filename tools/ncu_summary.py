@@ -35,7 +35,8 @@ cols = [
     ("smem/CTA KB", lambda r: val(r, "launch__shared_mem_per_block_dynamic", {"byte": 1 / 1024, "kbyte": 1.0}.get(
         units[idx.get("launch__shared_mem_per_block_dynamic", 0)].lower(), 1.0), "%.1f")),
     ("warps active %", lambda r: val(r, "sm__warps_active.avg.pct_of_peak_sustained_active", 1, "%.1f")),
-    ("issue active %", lambda r: val(r, "smsp__issue_active.avg.pct", 1, "%.1f")),
+    ("issue active %", lambda r: val(r, "smsp__issue_active.avg.pct" if "smsp__issue_active.avg.pct" in idx
+                                     else "sm__inst_issued.avg.pct_of_peak_sustained_active", 1, "%.1f")),
     ("IPC/SM", lambda r: val(r, "sm__inst_executed.avg.per_cycle_elapsed")),
     ("LSU wavefronts %", lambda r: val(r, "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed", 1, "%.1f")),
     ("LSU writeback %", lambda r: val(r, "l1tex__lsu_writeback_active.avg.pct_of_peak_sustained_elapsed", 1, "%.1f")),
