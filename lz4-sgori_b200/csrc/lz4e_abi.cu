@@ -535,7 +535,7 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 		 * block), a 2 KiB streaming window otherwise */
 		const uint32_t bound = max_in_bytes + max_in_bytes / 255u + 16u;
 
-		a.out_cap = bound <= 4352u ? ((bound + 15u) & ~15u) + 16u : 2048u;
+		a.out_cap = bound <= 4352u ? ((bound + 15u) & ~15u) + 16u : 1024u;
 		if (a.out_cap < 1024u)
 			a.out_cap = 1024u;
 		/* linear destinations are written in place: no staging, more
