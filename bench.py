@@ -29,8 +29,12 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools", "synth"))
 
 METRIC = "compress & decompress input GB/s at 4/64 KiB blocks, 1/2/4/8 B200, byte-identical"
+# ONE unit string for `value`, `e2e` and `cpu_baseline` in both arms (the driver only forms
+# ratios between equal units)
+UNIT = "GB/s of uncompressed input through compress+decompress (one step = both passes)"
 BLOCK = 4096
 BLOCKS_PER_GPU = 262144          # 1 GiB
 DST_STRIDE = 4224                # >= LZ4E_COMPRESSBOUND(4096) = 4128, multiple of 128
@@ -202,6 +206,7 @@ def event_ms(torch, fn, stream):
 # ----------------------------------------------------------------------------- product arm
 def run_ours(args):
     import torch
+    import lz4e_synth
     pkg = importlib.import_module("lz4-sgori_b200")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -228,8 +233,7 @@ def run_ours(args):
     (sbv, sit), (dbv, dit), (obv, oit) = cfg2_tables(pkg, d_src, d_dst, d_out, nb)
     t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
     d_rets, d_rets2 = ctx.dev_alloc(4 * nb), ctx.dev_alloc(4 * nb)
-    ctx.synth_fill_dev(t[0], t[1], nb, first_index=int(first), stream=sp)
-    ctx.sync(sp)
+    lz4e_synth.dev(local, t[0], t[1], nb, int(first), BLOCK)
     ctx.compress_dev(t[0], t[1], t[2], t[3], nb, BLOCK, d_rets, flags=pkg.DEV_DST_LINEAR, stream=sp)
     ctx.sync(sp)
     rets = ctx.download(d_rets, np.int32, nb)
@@ -259,11 +263,17 @@ def run_ours(args):
     # round-trip check on the warm-up result (size-independent property at full size)
     r2 = ctx.download(d_rets2, np.int32, nb)
     assert (r2 == BLOCK).all(), "round trip sizes"
-    a = torch.empty(0)  # noqa: F841
     src_t = ctx.download(d_src, np.uint8, min(in_bytes, 64 << 20))
     out_t = ctx.download(d_out, np.uint8, min(in_bytes, 64 << 20))
     assert np.array_equal(src_t, out_t), "round trip bytes"
     del src_t, out_t
+    # every 1024th block's source and compressed bytes, kept for the oracle byte-compare of
+    # the cpu_baseline leg (rank 0, N=1)
+    parity = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        parity = [(b, ctx.download(d_src + b * BLOCK, np.uint8, BLOCK),
+                   ctx.download(d_dst + b * DST_STRIDE, np.uint8, int(rets[b])))
+                  for b in range(0, nb, 1024)]
 
     def barrier():
         if dist is not None:
@@ -311,7 +321,7 @@ def run_ours(args):
         result = {
             "metric": METRIC,
             "value": round(job_in / (ms_per_step * 1e-3) / 1e9, 3),
-            "unit": "GB/s of uncompressed input through compress+decompress (one step = both passes)",
+            "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
@@ -337,11 +347,11 @@ def run_ours(args):
     for p in (d_src, d_dst, d_out, d_rets, d_rets2, d_cit, *t):
         ctx.dev_free(p)
 
-    if rank == 0 and not args.no_extra:
-        try:
-            result["extra"] = {"cfg3_64k": run_cfg3(torch, pkg, ctx, stream, args)}
-        except Exception as e:  # the headline line must still print
-            result["extra"] = {"cfg3_64k": {"error": repr(e)}}
+    if not args.no_extra:
+        # configs[2]/[3]: every rank runs its 2 GiB share of the 64 KiB workload
+        cfg3 = run_cfg3(torch, pkg, ctx, stream, args, dist, rank, world, local)
+        if rank == 0:
+            result["extra"] = {"cfg3_64k": cfg3}
     if rank == 0 and world == 1 and not args.no_extra:
         result["extra"]["cfg5_replay"] = run_replay()
     if not args.no_e2e:
@@ -351,7 +361,7 @@ def run_ours(args):
     elif rank == 0:
         result["e2e"] = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        result["cpu_baseline"] = cpu_baseline(pkg, budget_s=args.cpu_seconds)
+        result["cpu_baseline"] = cpu_baseline(pkg, budget_s=args.cpu_seconds, parity=parity)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -377,14 +387,20 @@ def profile_traffic(kernel):
 
 def run_replay():
     """BASELINE.json configs[4]: the C replay harness of the chunk layer / request path
-    (tools/replay/lz4e_replay.c), QD256 random 4-128 KiB writes/reads on this GPU."""
+    (tools/replay/lz4e_replay.c), QD256 random 4-128 KiB writes/reads on this GPU; --oracle
+    makes it compare every bio's compressed bytes with the reference (checker, untimed)."""
     import subprocess
     exe = os.path.join(ROOT, "tools", "replay", "lz4e_replay")
     try:
         if not os.path.exists(exe):
             subprocess.run(["make", "-C", os.path.dirname(exe)], check=True, capture_output=True)
-        out = subprocess.run([exe, "--arena-bios", "--batches", "48"], capture_output=True,
-                             text=True, timeout=120)
+        cmd = [exe, "--arena-bios", "--batches", "48"]
+        for so in (os.path.join(ROOT, "oracle", "_ref", "liblz4e_ref.so"),
+                   os.path.join(ROOT, "oracle", "_build", "liblz4e_port.so")):
+            if os.path.exists(so):
+                cmd += ["--oracle", so]
+                break
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=180)
         if out.returncode != 0:
             return {"error": "rc=%d %s" % (out.returncode, out.stderr[-300:])}
         return json.loads(out.stdout.strip().splitlines()[-1])
@@ -392,51 +408,97 @@ def run_replay():
         return {"error": repr(e)}
 
 
-def run_cfg3(torch, pkg, ctx, stream, args):
-    """2 GiB subset of config 3 on one GPU: 64 KiB blocks, 16 odd segments both sides."""
+def run_cfg3(torch, pkg, ctx, stream, args, dist, rank, world, local):
+    """configs[2] + configs[3]: 64 KiB blocks over 16 odd, non-contiguous segments on both
+    sides, mid-bvec iterator start (byU32).  EVERY rank runs CFG3_BLOCKS blocks (2 GiB; 8 ranks
+    = the full 16 GiB), sharded by block index, bracketed by barriers; the slowest rank's
+    kernel times count and the GB/s are whole-job aggregates."""
+    import lz4e_synth
     sp = stream.cuda_stream
     nb = CFG3_BLOCKS
+    first = rank * nb
     bound = pkg.compress_bound(CFG3_SIZE)
     region = nb * 16 * 3 * 4096
-    d_src, d_dst, d_out = ctx.dev_alloc(region), ctx.dev_alloc(region), ctx.dev_alloc(region)
-    sbv, sit, _ = cfg3_tables(pkg, d_src, nb, CFG3_SIZE, CFG3_SIZE, 0)
-    dbv, dit, _ = cfg3_tables(pkg, d_dst, nb, bound, bound, 11)
-    obv, oit, _ = cfg3_tables(pkg, d_out, nb, CFG3_SIZE, CFG3_SIZE, 5)
-    t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
-    d_rets, d_rets2 = ctx.dev_alloc(4 * nb), ctx.dev_alloc(4 * nb)
-    ctx.synth_fill_dev(t[0], t[1], nb, first_index=0, stream=sp)
-    ctx.compress_dev(t[0], t[1], t[2], t[3], nb, CFG3_SIZE, d_rets, flags=pkg.DEV_NO_BYU16, stream=sp)
-    ctx.sync(sp)
-    rets = ctx.download(d_rets, np.int32, nb)
-    assert (rets > 0).all()
-    cit = dit.copy()
-    cit["bi_size"] = rets.astype(np.uint32)
-    d_cit = ctx.upload(cit)
-    cms, dms = [], []
-    for it in range(2 + 3):
-        ec = event_ms(torch, lambda: ctx.compress_dev(t[0], t[1], t[2], t[3], nb, CFG3_SIZE, d_rets,
-                                                      flags=pkg.DEV_NO_BYU16, stream=sp), stream)
-        ed = event_ms(torch, lambda: ctx.decompress_dev(t[2], d_cit, t[4], t[5], nb, int(rets.max()),
-                                                        CFG3_SIZE, d_rets2, stream=sp), stream)
+    err = None
+    try:
+        d_src, d_dst, d_out = ctx.dev_alloc(region), ctx.dev_alloc(region), ctx.dev_alloc(region)
+        sbv, sit, _ = cfg3_tables(pkg, d_src, nb, CFG3_SIZE, CFG3_SIZE, 0)
+        dbv, dit, _ = cfg3_tables(pkg, d_dst, nb, bound, bound, 11)
+        obv, oit, _ = cfg3_tables(pkg, d_out, nb, CFG3_SIZE, CFG3_SIZE, 5)
+        t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
+        d_rets, d_rets2 = ctx.dev_alloc(4 * nb), ctx.dev_alloc(4 * nb)
+        lz4e_synth.dev(local, t[0], t[1], nb, first, CFG3_SIZE)
+        ctx.compress_dev(t[0], t[1], t[2], t[3], nb, CFG3_SIZE, d_rets, flags=pkg.DEV_NO_BYU16, stream=sp)
         ctx.sync(sp)
-        if it >= 2:
-            cms.append(ec[0].elapsed_time(ec[1]))
-            dms.append(ed[0].elapsed_time(ed[1]))
-    r2 = ctx.download(d_rets2, np.int32, nb)
-    assert (r2 == CFG3_SIZE).all(), "64k round trip sizes"
-    nbytes, cbytes = nb * CFG3_SIZE, int(rets.sum())
+        rets = ctx.download(d_rets, np.int32, nb)
+        assert (rets > 0).all()
+        cit = dit.copy()
+        cit["bi_size"] = rets.astype(np.uint32)
+        d_cit = ctx.upload(cit)
+        cms, dms = [], []
+        warm, reps = 2, 4
+        for it in range(warm + reps):
+            if it == warm:
+                if dist is not None:
+                    dist.barrier()
+                torch.cuda.synchronize()
+            ec = event_ms(torch, lambda: ctx.compress_dev(t[0], t[1], t[2], t[3], nb, CFG3_SIZE, d_rets,
+                                                          flags=pkg.DEV_NO_BYU16, stream=sp), stream)
+            ed = event_ms(torch, lambda: ctx.decompress_dev(t[2], d_cit, t[4], t[5], nb, int(rets.max()),
+                                                            CFG3_SIZE, d_rets2, stream=sp), stream)
+            ctx.sync(sp)
+            if it >= warm:
+                cms.append(ec[0].elapsed_time(ec[1]))
+                dms.append(ed[0].elapsed_time(ed[1]))
+        r2 = ctx.download(d_rets2, np.int32, nb)
+        assert (r2 == CFG3_SIZE).all(), "64k round trip sizes"
+        # bit-exact round trip of a sample of blocks (gathered through the segment tables)
+        for b in range(0, nb, 4096):
+            assert np.array_equal(_gather_dev(ctx, sbv, sit, b, CFG3_SIZE),
+                                  _gather_dev(ctx, obv, oit, b, CFG3_SIZE)), "64k round trip bytes"
+        for p in (d_src, d_dst, d_out, d_rets, d_rets2, d_cit, *t):
+            ctx.dev_free(p)
+        c_ms, d_ms, cbytes = float(np.mean(cms)), float(np.mean(dms)), int(rets.sum())
+    except Exception as e:  # the headline line must still print
+        err, c_ms, d_ms, cbytes = repr(e), 0.0, 0.0, 0
+    if dist is not None:
+        tt = torch.tensor([c_ms, d_ms, 1.0 if err else 0.0], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        c_ms, d_ms, bad = [float(x) for x in tt.tolist()]
+        cb = torch.tensor([cbytes], device=f"cuda:{local}", dtype=torch.int64)
+        dist.all_reduce(cb)
+        cbytes = int(cb.item())
+        if bad and not err:
+            err = "another rank failed"
+    if err:
+        return {"error": err}
+    nbytes = nb * CFG3_SIZE * world
     peak, _ = peaks()
-    c_ms, d_ms = float(np.mean(cms)), float(np.mean(dms))
-    for p in (d_src, d_dst, d_out, d_rets, d_rets2, d_cit, *t):
-        ctx.dev_free(p)
-    return {"workload": "configs[2] subset: %d x 64 KiB blocks (2 GiB), 16 odd non-contiguous "
-                        "segments per side, mid-bvec start (byU32)" % nb,
+    return {"workload": "configs[2]/[3]: %d x 64 KiB blocks per GPU (2 GiB/GPU, %d GiB in all), 16 odd "
+                        "non-contiguous segments per side, mid-bvec start (byU32); every rank runs "
+                        "its share, barrier-bracketed, slowest rank counts" % (nb, 2 * world),
+            "n_gpus": world,
             "compress_gbs": round(nbytes / (c_ms * 1e-3) / 1e9, 3),
             "decompress_gbs": round(nbytes / (d_ms * 1e-3) / 1e9, 3),
+            "decompress_compressed_in_gbs": round(cbytes / (d_ms * 1e-3) / 1e9, 3),
             "ratio": round(nbytes / cbytes, 4),
             "kernel_ms": {"compress": round(c_ms, 3), "decompress": round(d_ms, 3)},
-            "decompress_roofline_frac": round((nbytes + cbytes) / (d_ms * 1e-3) / 1e9 / peak, 5),
-            "compress_roofline_frac": round((nbytes + cbytes) / (c_ms * 1e-3) / 1e9 / peak, 5)}
+            "algorithmic_bytes_per_launch": int((nbytes + cbytes) // world),
+            "decompress_roofline_frac": round((nbytes + cbytes) / (d_ms * 1e-3) / 1e9 / (peak * world), 5),
+            "compress_roofline_frac": round((nbytes + cbytes) / (c_ms * 1e-3) / 1e9 / (peak * world), 5)}
+
+
+def _gather_dev(ctx, bv, it, b, nbytes):
+    """Linear bytes of block b from device memory, walking its dev_bvec list."""
+    out, i, done = [], int(it["first"][b]) + int(it["bi_idx"][b]), int(it["bi_bvec_done"][b])
+    left = nbytes
+    while left > 0:
+        take = min(left, int(bv["len"][i]) - done)
+        out.append(ctx.download(int(bv["addr"][i]) + done, np.uint8, take))
+        left -= take
+        done = 0
+        i += 1
+    return np.concatenate(out) if out else np.zeros(0, np.uint8)
 
 
 def run_e2e(torch, pkg, ctx, args, dist=None, rank=0, world=1, local=0):
@@ -465,10 +527,8 @@ def run_e2e(torch, pkg, ctx, args, dist=None, rank=0, world=1, local=0):
         return sg.Layout(arena, bv, idx.copy(), it, arena.npages)
     src, dst, out = lay(src_arena, BLOCK, BLOCK), lay(dst_arena, DST_STRIDE, bound), \
         lay(out_arena, BLOCK, BLOCK)
-    mem = src_arena.mem[:nb * BLOCK].reshape(nb, BLOCK)
-    for b in range(nb):
-        g = rank * nb + b  # global block index: class and seed
-        pkg.lib().lz4e_b200_synth_fill_host(mem[b].ctypes.data, BLOCK, g & 3, g)
+    import lz4e_synth
+    lz4e_synth.host_blocks(src_arena.mem, BLOCK, BLOCK, nb, first=rank * nb)  # global index = class, seed
     creqs, keep1 = pkg.make_reqs(src, dst)
     # the decompress requests read the compressed blocks where compress left them; only the
     # compressed sizes change from step to step
@@ -507,30 +567,30 @@ def run_e2e(torch, pkg, ctx, args, dist=None, rank=0, world=1, local=0):
     for a in (src_arena, dst_arena, out_arena):
         a.close()
     return {"value": round(world * nb * BLOCK / dt / 1e9, 3),
-            "unit": "GB/s of uncompressed input through compress+decompress, host buffers",
+            "unit": UNIT, "buffers": "host (pinned page arenas); copies inside the timed region",
             "blocks": world * nb, "ms_per_step": round(dt * 1e3, 3),
             "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
             "api": "lz4e_b200_compress_batch + lz4e_b200_decompress_batch (pinned page arenas)"}
 
 
 # ----------------------------------------------------------------------------- CPU arms
-def cpu_sample(pkg, nblocks, first_index=0):
-    """Host copy of the first `nblocks` blocks of the config-2 workload + bio_vec tables."""
-    sg = pkg.sg
+# Nothing below loads the product library: the reference's C code (oracle/_ref, else the
+# oracle port) is what runs, and the synthetic contents come from the oracle driver's own
+# copy of the generator (tools/synth/lz4e_synth.h).
+def cpu_sample(sg, lib, nblocks, threads, first_index=0):
+    """Host copy of `nblocks` blocks of the config-2 workload + bio_vec tables."""
+    from oracle import oracle
     arena = sg.HostArena(nblocks + 1)
     specs = [sg.segs_single(BLOCK)] * nblocks
     src = sg.layout_from_segments(arena, [dict(s, gap=0) for s in specs])
-    mem = arena.mem[:nblocks * BLOCK].reshape(nblocks, BLOCK)
-    for b in range(nblocks):
-        pkg.lib().lz4e_b200_synth_fill_host(mem[b].ctypes.data, BLOCK, (first_index + b) & 3,
-                                            first_index + b)
-    bound = pkg.compress_bound(BLOCK)
+    oracle.synth_blocks(lib, arena.mem, BLOCK, BLOCK, nblocks, first=first_index, nthreads=threads)
+    bound = sg.compress_bound(BLOCK)
     darena = sg.HostArena(nblocks * 2 + 1)
     dst = sg.layout_from_segments(darena, [dict(sg.segs_single(bound), gap=0)] * nblocks)
     return src, dst
 
 
-def cpu_run(pkg, lib, src, dst, threads):
+def cpu_run(lib, src, dst, threads):
     """One CPU step on a sample: compress every block, then decompress every block."""
     from oracle import oracle
     n = src.nblocks()
@@ -546,23 +606,110 @@ def cpu_run(pkg, lib, src, dst, threads):
     return t_c, t_d
 
 
-def cpu_baseline(pkg, budget_s=12.0):
+def cpu_cfg3(sg, lib, threads, nblocks):
+    """The reference C path on a subset of configs[2]: 64 KiB blocks over 16 odd segments
+    (compress: SG source and destination as on the GPU; decompress: the reference decoder only
+    takes contiguous buffers, so it runs on the linearised compressed blocks)."""
     from oracle import oracle
+
+    class _Np:  # cfg3_tables only needs the dtypes
+        DEV_BVEC = np.dtype([("addr", "<u8"), ("len", "<u4"), ("rsvd", "<u4")])
+        DEV_ITER = np.dtype([("first", "<u4"), ("bi_size", "<u4"), ("bi_idx", "<u4"),
+                             ("bi_bvec_done", "<u4")])
+    bound = sg.compress_bound(CFG3_SIZE)
+    region = nblocks * 16 * 3 * 4096
+    smem = np.zeros(region + 4096, dtype=np.uint8)
+    dmem = np.zeros(region + 4096, dtype=np.uint8)
+    sbase = (smem.ctypes.data + 4095) & ~4095
+    dbase = (dmem.ctypes.data + 4095) & ~4095
+
+    def host_tables(base, size, cap, salt):
+        bv, it, _ = cfg3_tables(_Np, base, nblocks, size, cap, salt)
+        hv = np.zeros(len(bv), dtype=oracle.BIO_VEC)
+        hv["bv_page"] = bv["addr"] & ~np.uint64(4095)
+        hv["bv_offset"] = (bv["addr"] & np.uint64(4095)).astype(np.uint32)
+        hv["bv_len"] = bv["len"]
+        hi = np.zeros(nblocks, dtype=oracle.BVEC_ITER)
+        hi["bi_size"] = it["bi_size"]
+        hi["bi_bvec_done"] = it["bi_bvec_done"]
+        return bv, it, hv, hi, it["first"].astype(np.uint64)
+    sbv, sit, shv, shi, sfirst = host_tables(sbase, CFG3_SIZE, CFG3_SIZE, 0)
+    dbv, dit, dhv, dhi, dfirst = host_tables(dbase, bound, bound, 11)
+    # contents: generate linear, scatter into the segments
+    lin = np.zeros(nblocks * CFG3_SIZE, dtype=np.uint8)
+    oracle.synth_blocks(lib, lin, CFG3_SIZE, CFG3_SIZE, nblocks, first=0, nthreads=threads)
+
+    def walk(bv, it, base_addr, mem, b, nbytes, data=None):
+        out, i, done, left, pos = [], int(it["first"][b]), int(it["bi_bvec_done"][b]), nbytes, 0
+        off0 = mem.ctypes.data
+        while left > 0:
+            take = min(left, int(bv["len"][i]) - done)
+            o = int(bv["addr"][i]) + done - off0
+            if data is None:
+                out.append(mem[o:o + take])
+            else:
+                mem[o:o + take] = data[pos:pos + take]
+            left, pos, done, i = left - take, pos + take, 0, i + 1
+        return np.concatenate(out) if data is None else None
+    for b in range(nblocks):
+        walk(sbv, sit, sbase, smem, b, CFG3_SIZE, lin[b * CFG3_SIZE:(b + 1) * CFG3_SIZE])
+    rets, t_c = oracle.compress_batch(lib, shv, sfirst, shi, dhv, dfirst, dhi, nthreads=threads)
+    assert (rets > 0).all()
+    comp = [walk(dbv, dit, dbase, dmem, b, int(rets[b])) for b in range(nblocks)]
+    cbuf = np.concatenate(comp + [np.zeros(64, np.uint8)])
+    coff = np.concatenate([[0], np.cumsum(rets)[:-1]]).astype(np.uint64)
+    out = np.zeros(nblocks * CFG3_SIZE + 64, dtype=np.uint8)
+    r2, t_d = oracle.decompress_batch(lib, cbuf, coff, rets, out,
+                                      np.arange(nblocks, dtype=np.uint64) * np.uint64(CFG3_SIZE),
+                                      np.full(nblocks, CFG3_SIZE, dtype=np.int32), nthreads=threads)
+    assert (r2 == CFG3_SIZE).all() and np.array_equal(out[:nblocks * CFG3_SIZE], lin)
+    nbytes = nblocks * CFG3_SIZE
+    return {"value": round(nbytes / (t_c + t_d) / 1e9, 4), "unit": UNIT,
+            "compress_gbs": round(nbytes / t_c / 1e9, 4), "decompress_gbs": round(nbytes / t_d / 1e9, 4),
+            "sample": "first %d blocks (%d MiB) of the configs[2] workload; decompress on the "
+                      "linearised compressed blocks (the reference decoder is contiguous-only)"
+                      % (nblocks, nbytes >> 20)}
+
+
+def cpu_baseline(pkg, budget_s=12.0, parity=None):
+    from oracle import oracle
+    sg = pkg.sg
     lib = oracle.load("auto")
     threads = os.cpu_count() or 1
-    src, dst = cpu_sample(pkg, 1024)
-    t_c, t_d = cpu_run(pkg, lib, src, dst, threads)
+    kind = "reference" if lib.kind == "reference" else "port"
+    src, dst = cpu_sample(sg, lib, 1024, threads)
+    t_c, t_d = cpu_run(lib, src, dst, threads)
     per_block = (t_c + t_d) / 1024
     n = int(min(max(budget_s / max(per_block, 1e-9), 2048), 65536))
-    src, dst = cpu_sample(pkg, n)
-    t_c, t_d = cpu_run(pkg, lib, src, dst, threads)
+    src, dst = cpu_sample(sg, lib, n, threads)
+    t_c, t_d = cpu_run(lib, src, dst, threads)
     nbytes = n * BLOCK
-    return {"value": round(nbytes / (t_c + t_d) / 1e9, 4),
-            "unit": "GB/s of uncompressed input through compress+decompress",
-            "cores": threads, "kind": "reference" if lib.kind == "reference" else "port",
-            "sample": "first %d blocks (%d MiB) of the configs[1] workload, one block per task, "
-                      "one thread per core with its own wrkmem" % (n, nbytes >> 20),
-            "compress_gbs": round(nbytes / t_c / 1e9, 4), "decompress_gbs": round(nbytes / t_d / 1e9, 4)}
+    res = {"value": round(nbytes / (t_c + t_d) / 1e9, 4), "unit": UNIT,
+           "cores": threads, "kind": kind,
+           "sample": "first %d blocks (%d MiB) of the configs[1] workload, one block per task, "
+                     "one thread per core with its own wrkmem" % (n, nbytes >> 20),
+           "compress_gbs": round(nbytes / t_c / 1e9, 4), "decompress_gbs": round(nbytes / t_d / 1e9, 4)}
+    try:
+        res["cfg3_64k"] = cpu_cfg3(sg, lib, threads, 1024)
+    except Exception as e:
+        res["cfg3_64k"] = {"error": repr(e)}
+    if parity:
+        # the oracle as the checker: the GPU's compressed bytes of every 1024th block of the
+        # timed workload against the reference's, byte for byte
+        k = len(parity)
+        arena = sg.HostArena(k + 1)
+        ps = sg.layout_from_segments(arena, [dict(sg.segs_single(BLOCK), gap=0)] * k)
+        for i, (_, data, _) in enumerate(parity):
+            arena.mem[i * BLOCK:(i + 1) * BLOCK] = data
+        darena = sg.HostArena(2 * k + 1)
+        pd = sg.layout_from_segments(darena, [dict(sg.segs_single(sg.compress_bound(BLOCK)), gap=0)] * k)
+        r, _ = oracle.compress_batch(lib, ps.bvecs, ps.first, ps.iters, pd.bvecs, pd.first, pd.iters,
+                                     nthreads=threads)
+        same = all(int(r[i]) == len(c) and np.array_equal(pd.read_block(i, int(r[i])), c)
+                   for i, (_, _, c) in enumerate(parity))
+        res["parity_sample"] = {"blocks": k, "byte_identical": bool(same), "checker": kind}
+        assert same, "GPU output differs from the oracle on the parity sample"
+    return res
 
 
 def run_reference(args):
@@ -570,40 +717,46 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    pkg = importlib.import_module("lz4-sgori_b200")
+    pkg = importlib.import_module("lz4-sgori_b200")  # pure-Python layout helpers only (pkg.sg);
+    sg = pkg.sg                                       # the product .so is never loaded here
     from oracle import oracle
     lib = oracle.load("auto")
     threads = os.cpu_count() or 1
     world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
-    src, dst = cpu_sample(pkg, 512)
-    t_c, t_d = cpu_run(pkg, lib, src, dst, threads)
+    src, dst = cpu_sample(sg, lib, 512, threads)
+    t_c, t_d = cpu_run(lib, src, dst, threads)
     per_block = (t_c + t_d) / 512
     total_steps = args.steps + args.warmup
     n = int(min(max(60.0 / total_steps / max(per_block, 1e-9), 1024), 32768))
-    src, dst = cpu_sample(pkg, n)
+    src, dst = cpu_sample(sg, lib, n, threads)
     for _ in range(args.warmup):
-        cpu_run(pkg, lib, src, dst, threads)
+        cpu_run(lib, src, dst, threads)
     tc = td = 0.0
     for _ in range(args.steps):
-        a, b = cpu_run(pkg, lib, src, dst, threads)
+        a, b = cpu_run(lib, src, dst, threads)
         tc, td = tc + a, td + b
     nbytes = n * BLOCK * args.steps
     val = round(nbytes / (tc + td) / 1e9, 4)
-    unit = "GB/s of uncompressed input through compress+decompress (one step = both passes)"
     kind = "reference" if lib.kind == "reference" else "port"
     sample = ("each step = first %d blocks (%d MiB) of the configs[1] workload; whole job is %d GiB"
               % (n, (n * BLOCK) >> 20, world))
+    cb = {"value": val, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample}
+    try:
+        cb["cfg3_64k"] = cpu_cfg3(sg, lib, threads, 512)
+    except Exception as e:
+        cb["cfg3_64k"] = {"error": repr(e)}
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": val, "unit": unit, "n_gpus": world,
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round((tc + td) / args.steps * 1e3, 3), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "configs[1]: 4 KiB blocks, 1 bvec each (byU16), class = block index "
-                               "mod 4; CPU arm runs a bounded sample per step",
+        "config": {"workload": "configs[1]: %d x 4 KiB blocks per GPU (1 GiB/GPU), 1 bvec each "
+                               "(byU16), class = block index mod 4 (text/random/sparse/mixed), "
+                               "dst capacity LZ4E_COMPRESSBOUND" % BLOCKS_PER_GPU,
                    "sample": sample},
         "compress_gbs": round(nbytes / tc / 1e9, 4), "decompress_gbs": round(nbytes / td / 1e9, 4),
-        "cpu_baseline": {"value": val, "unit": unit, "cores": threads, "kind": kind, "sample": sample},
-        "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "cpu_baseline": cb,
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
 

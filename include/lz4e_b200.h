@@ -170,17 +170,6 @@ int lz4e_b200_compress_compact_dev(lz4e_b200_ctx *ctx, void *stream,
 				   uint32_t max_in_bytes, uint32_t flags,
 				   int32_t *rets, uint64_t *offsets);
 
-/* Fill SG blocks with the synthetic benchmark contents of
- * lz4-sgori_b200/csrc/lz4e_synth.h: class = (first_index + b) & 3, seed =
- * first_index + b. */
-int lz4e_b200_synth_fill_dev(lz4e_b200_ctx *ctx, void *stream,
-			     const struct lz4e_b200_dev_bvec *bvecs,
-			     const struct lz4e_b200_dev_iter *iters,
-			     uint32_t nblocks, uint32_t first_index);
-/* the same generator on the host */
-void lz4e_b200_synth_fill_host(uint8_t *buf, uint32_t n, uint32_t cls,
-			       uint32_t seed);
-
 /* ---- raw memory helpers for the C host library --------------------------- */
 void *lz4e_b200_dev_alloc(lz4e_b200_ctx *ctx, size_t bytes);
 void lz4e_b200_dev_free(lz4e_b200_ctx *ctx, void *p);

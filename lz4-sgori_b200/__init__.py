@@ -72,8 +72,6 @@ def lib():
         "lz4e_b200_decompress_dev": (i32, [vp, vp, vp, vp, vp, vp, u32, u32, u32, u32, vp]),
         "lz4e_b200_compress_compact_dev": (i32, [vp, vp, vp, vp, vp, u32, u32, u64, u32, u32,
                                                  u32, vp, vp]),
-        "lz4e_b200_synth_fill_dev": (i32, [vp, vp, vp, vp, u32, u32]),
-        "lz4e_b200_synth_fill_host": (None, [vp, u32, u32, u32]),
         "lz4e_b200_dev_alloc": (vp, [vp, sz]),
         "lz4e_b200_dev_free": (None, [vp, vp]),
         "lz4e_b200_host_alloc": (vp, [vp, sz]),
@@ -109,12 +107,6 @@ def shard_range(nblocks, rank, world):
     first, count = ctypes.c_uint64(), ctypes.c_uint64()
     lib().lz4e_b200_shard_range(nblocks, rank, world, ctypes.byref(first), ctypes.byref(count))
     return first.value, count.value
-
-
-def synth_host(n, cls, seed):
-    buf = np.zeros(max(int(n), 1), dtype=np.uint8)
-    lib().lz4e_b200_synth_fill_host(buf.ctypes.data, int(n), int(cls), int(seed))
-    return buf[:n]
 
 
 def _p(a):
@@ -199,10 +191,6 @@ class Context:
         self.check(lib().lz4e_b200_compress_compact_dev(
             self.h, _p(stream), _p(sbv), _p(sit), _p(dbv), dst_nbvecs, dst_done, dst_cap, nblocks,
             max_in, flags, _p(rets), _p(offsets)), "compress_compact_dev")
-
-    def synth_fill_dev(self, bv, it, nblocks, first_index=0, stream=None):
-        self.check(lib().lz4e_b200_synth_fill_dev(self.h, _p(stream), _p(bv), _p(it), nblocks,
-                                                  first_index), "synth_fill_dev")
 
     # ---- host-level calls ----
     def compress_batch(self, reqs, flags=0):

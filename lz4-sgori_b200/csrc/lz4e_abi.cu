@@ -18,7 +18,6 @@
 #include "lz4e_compress_body.cuh"
 #include "lz4e_decompress_body.cuh"
 #include "lz4e_kernels.h"
-#include "lz4e_synth.h"
 
 #define CTL_COUNTERS 256
 #define CTL_FAULTS CTL_COUNTERS
@@ -734,45 +733,6 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 	}
 	ctx->launches++;
 	return LZ4E_B200_OK;
-}
-
-int lz4e_b200_synth_fill_dev(lz4e_b200_ctx *ctx, void *stream,
-			     const struct lz4e_b200_dev_bvec *bvecs,
-			     const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
-			     uint32_t first_index)
-{
-	/* generate into linear slots, then scatter into the SG layout; chunked so
-	 * the linear scratch stays small */
-	const uint32_t stride = 65536u; /* blocks up to 64 KiB */
-	const uint32_t chunk = 8192u;
-	cudaStream_t s;
-	int rc;
-
-	if (!ctx)
-		return LZ4E_B200_ENODEV;
-	cudaSetDevice(ctx->device);
-	s = pick(ctx, stream);
-	rc = ensure_scratch(ctx, (size_t)chunk * stride);
-	if (rc)
-		return rc;
-	for (uint32_t b0 = 0; b0 < nblocks; b0 += chunk) {
-		const uint32_t nb = nblocks - b0 < chunk ? nblocks - b0 : chunk;
-
-		ctx->launches += 2;
-		if (lz4e_launch_synth(ctx->scratch, stride, iters + b0, nb, first_index + b0, s) ||
-		    lz4e_launch_scatter(ctx->scratch, stride, bvecs, iters + b0, nb,
-					ctx->sm_count, s)) {
-			set_err(ctx, "synth launch failed: %s",
-				cudaGetErrorString(cudaGetLastError()));
-			return LZ4E_B200_EIO;
-		}
-	}
-	return LZ4E_B200_OK;
-}
-
-void lz4e_b200_synth_fill_host(uint8_t *buf, uint32_t n, uint32_t cls, uint32_t seed)
-{
-	lz4e_synth_block(buf, n, cls, seed);
 }
 
 void lz4e_b200_shard_range(uint64_t nblocks, uint32_t rank, uint32_t world,

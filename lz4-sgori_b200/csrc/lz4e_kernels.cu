@@ -9,7 +9,6 @@
 #include "lz4e_decompress_body.cuh"
 #include "lz4e_decompress_lane.cuh"
 #include "lz4e_kernels.h"
-#include "lz4e_synth.h"
 
 extern __shared__ __align__(16) uint8_t lz4e_smem[];
 
@@ -48,36 +47,6 @@ lz4e_decompress_lane_kernel(const lz4e_decompress_args a)
 	const uint32_t slot0 = (blockIdx.x * LZ4E_D_WARPS + warp) * 32u;
 
 	lz4e_decompress_lanes(a, &sm[warp], slot0, threadIdx.x & 31);
-}
-
-/* ---- synthetic contents: one thread writes one linear block --------------- */
-__global__ void lz4e_synth_kernel(uint8_t *lin, uint32_t stride,
-				  const struct lz4e_b200_dev_iter *iters,
-				  uint32_t nblocks, uint32_t first_index)
-{
-	const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-
-	if (b >= nblocks)
-		return;
-	lz4e_synth_block(lin + (size_t)b * stride, iters[b].bi_size,
-			 (first_index + b) & 3u, first_index + b);
-}
-
-/* linear slots -> SG blocks (also used to pack compacted output), one warp
- * per block */
-__global__ void __launch_bounds__(128)
-lz4e_scatter_kernel(const uint8_t *lin, uint32_t stride,
-		    const struct lz4e_b200_dev_bvec *bvecs,
-		    const struct lz4e_b200_dev_iter *iters, uint32_t nblocks)
-{
-	const uint32_t lane = threadIdx.x & 31;
-
-	for (uint32_t b = blockIdx.x * 4 + (threadIdx.x >> 5); b < nblocks;
-	     b += gridDim.x * 4) {
-		lz4e_cursor c = lz4e_cursor_init(bvecs, iters[b]);
-
-		lz4e_scatter<32>(c, lin + (size_t)b * stride, iters[b].bi_size, lane);
-	}
 }
 
 /* ------------------------------------------------------------------------- */
@@ -297,29 +266,4 @@ int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
 	default:
 		return launch_decompress_t<32, false>(a, sm_count, stream, grid_limit, grid_out);
 	}
-}
-
-int lz4e_launch_synth(uint8_t *lin, uint32_t stride,
-		      const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
-		      uint32_t first_index, cudaStream_t stream)
-{
-	lz4e_synth_kernel<<<(nblocks + 63) / 64, 64, 0, stream>>>(lin, stride, iters,
-								  nblocks, first_index);
-	return cudaGetLastError() == cudaSuccess ? 0 : -1;
-}
-
-int lz4e_launch_scatter(const uint8_t *lin, uint32_t stride,
-			const struct lz4e_b200_dev_bvec *bvecs,
-			const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
-			int sm_count, cudaStream_t stream)
-{
-	long long grid = ((long long)nblocks + 3) / 4;
-
-	if (grid > (long long)sm_count * 16)
-		grid = (long long)sm_count * 16;
-	if (grid < 1)
-		grid = 1;
-	lz4e_scatter_kernel<<<(unsigned)grid, 128, 0, stream>>>(lin, stride, bvecs, iters,
-								nblocks);
-	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

@@ -20,12 +20,5 @@ int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_co
 int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
 			   int sm_count, cudaStream_t stream, int grid_limit,
 			   int *grid_out);
-int lz4e_launch_synth(uint8_t *lin, uint32_t stride,
-		      const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
-		      uint32_t first_index, cudaStream_t stream);
-int lz4e_launch_scatter(const uint8_t *lin, uint32_t stride,
-			const struct lz4e_b200_dev_bvec *bvecs,
-			const struct lz4e_b200_dev_iter *iters, uint32_t nblocks,
-			int sm_count, cudaStream_t stream);
 
 #endif

@@ -45,6 +45,9 @@ def _bind(path):
     lib.oracle_decompress_batch.restype = ctypes.c_double
     lib.oracle_decompress_batch.argtypes = [vp, vp, vp, vp, vp, vp, ctypes.c_int64, vp,
                                             ctypes.c_int]
+    lib.oracle_synth_blocks.restype = None
+    lib.oracle_synth_blocks.argtypes = [vp, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint64,
+                                        ctypes.c_uint64, ctypes.c_int]
     lib.LZ4E_decompress_safe.restype = ctypes.c_int
     lib.LZ4E_decompress_safe.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int]
     assert lib.oracle_sizeof_bio_vec() == 16
@@ -107,3 +110,10 @@ def decompress_batch(lib, src, src_off, src_len, dst, dst_off, dst_cap, nthreads
     secs = lib.oracle_decompress_batch(_p(src), _p(src_off), _p(src_len), _p(dst), _p(dst_off),
                                        _p(dst_cap), n, _p(rets), int(nthreads))
     return rets, secs
+
+
+def synth_blocks(lib, mem, stride, n, nblocks, first=0, nthreads=1):
+    """Benchmark contents (tools/synth/lz4e_synth.h) for nblocks blocks of n bytes at
+    mem[b * stride:]; class and seed from first + b."""
+    assert mem.dtype == np.uint8 and mem.nbytes >= (nblocks - 1) * stride + n
+    lib.oracle_synth_blocks(_p(mem), int(stride), int(n), int(nblocks), int(first), int(nthreads))

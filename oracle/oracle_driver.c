@@ -21,6 +21,10 @@
 
 #include <linux/bio.h>
 
+/* benchmark data generator (tools/synth), so that bench.py's CPU arm needs no
+ * other native library than this one */
+#include "../tools/synth/lz4e_synth.h"
+
 #define ORACLE_WRKMEM_BYTES 17440 /* LZ4E_MEM_COMPRESS, lz4e/include/lz4e.h:17-22 */
 
 int LZ4E_compress_default(const struct bio_vec *src, struct bio_vec *dst,
@@ -160,6 +164,53 @@ double oracle_decompress_batch(const char *src_base, const uint64_t *src_off,
 	j.nblocks = nblocks;
 	j.rets = rets;
 	return run_job(&j, nthreads);
+}
+
+struct synth_job {
+	uint8_t *base;
+	uint64_t stride, nblocks, first;
+	uint32_t n;
+	int64_t next;
+};
+
+static void *synth_worker(void *arg)
+{
+	struct synth_job *j = (struct synth_job *)arg;
+
+	for (;;) {
+		int64_t b = __atomic_fetch_add(&j->next, 64, __ATOMIC_RELAXED);
+		int64_t e = b + 64;
+
+		if (b >= (int64_t)j->nblocks)
+			break;
+		if (e > (int64_t)j->nblocks)
+			e = (int64_t)j->nblocks;
+		for (; b < e; b++)
+			lz4e_synth_block(j->base + (uint64_t)b * j->stride, j->n,
+					 (uint32_t)((j->first + (uint64_t)b) & 3u),
+					 (uint32_t)(j->first + (uint64_t)b));
+	}
+	return NULL;
+}
+
+/* synthetic benchmark contents: nblocks blocks of n bytes at base + b * stride,
+ * class (first + b) & 3, seed first + b */
+void oracle_synth_blocks(uint8_t *base, uint64_t stride, uint32_t n, uint64_t nblocks,
+			 uint64_t first, int nthreads)
+{
+	struct synth_job j = { base, stride, nblocks, first, n, 0 };
+	pthread_t th[256];
+	int i;
+
+	if (nthreads < 1)
+		nthreads = 1;
+	if (nthreads > 256)
+		nthreads = 256;
+	for (i = 1; i < nthreads; i++)
+		pthread_create(&th[i], NULL, synth_worker, &j);
+	synth_worker(&j);
+	for (i = 1; i < nthreads; i++)
+		pthread_join(th[i], NULL);
 }
 
 /* layout probes so the Python side can assert its ctypes mirror is right */

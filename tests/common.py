@@ -1,5 +1,7 @@
 """Shared helpers for the tests: workload construction and oracle runs."""
 import importlib
+import os
+import sys
 
 import numpy as np
 
@@ -7,10 +9,19 @@ from oracle import oracle
 
 pkg = importlib.import_module("lz4-sgori_b200")
 sg = pkg.sg
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                "tools", "synth"))
+import lz4e_synth  # noqa: E402  (benchmark data generator, tools/synth)
 
 
 def synth(n, cls, seed):
-    return pkg.synth_host(n, cls, seed)
+    return lz4e_synth.host(n, cls, seed)
+
+
+def synth_fill_dev(ctx, d_bv, d_it, nblocks, max_bytes, first_index=0):
+    """Device-resident blocks filled by the generator's own kernels (tools/synth)."""
+    ctx.sync()
+    lz4e_synth.dev(ctx.device, d_bv, d_it, nblocks, first_index, max_bytes)
 
 
 def lcg_text(n, seed=12345):

@@ -39,7 +39,7 @@ def test_config2_full_size(ctx, ref_lib):
     (sbv, sit), (dbv, dit), (obv, oit) = bench.cfg2_tables(pkg, d_src, d_dst, d_out, n)
     t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
     r1, r2 = ctx.dev_alloc(4 * n), ctx.dev_alloc(4 * n)
-    ctx.synth_fill_dev(t[0], t[1], n)
+    common.synth_fill_dev(ctx, t[0], t[1], n, B)
     ctx.compress_dev(t[0], t[1], t[2], t[3], n, B, r1, flags=pkg.DEV_DST_LINEAR)
     ctx.sync()
     rets = ctx.download(r1, np.int32, n)
@@ -83,7 +83,7 @@ def test_config3_one_gpu_share(ctx, ref_lib):
     obv, oit, _ = bench.cfg3_tables(pkg, c, n, S, S, 5)
     t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
     r1, r2 = ctx.dev_alloc(4 * n), ctx.dev_alloc(4 * n)
-    ctx.synth_fill_dev(t[0], t[1], n)
+    common.synth_fill_dev(ctx, t[0], t[1], n, S)
     ctx.compress_dev(t[0], t[1], t[2], t[3], n, S, r1, flags=pkg.DEV_NO_BYU16)
     ctx.sync()
     rets = ctx.download(r1, np.int32, n)

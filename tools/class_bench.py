@@ -9,6 +9,8 @@ import time
 import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "synth"))
+import lz4e_synth  # noqa: E402  (tools/synth: benchmark data generator)
 import bench  # noqa: E402
 
 pkg = importlib.import_module("lz4-sgori_b200")
@@ -25,7 +27,7 @@ def main():
     host = np.zeros((n, 4096), dtype=np.uint8)
     for cls in range(4):
         for b in range(n):
-            pkg.lib().lz4e_b200_synth_fill_host(host[b].ctypes.data, 4096, cls, 4 * b + cls)
+            lz4e_synth.lib().lz4e_synth_fill_host(host[b].ctypes.data, 4096, cls, 4 * b + cls)
         ctx.check(pkg.lib().lz4e_b200_copy_h2d(ctx.h, None, d_src, host.ctypes.data, n * 4096), "h2d")
         ctx.sync()
         ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1, flags=pkg.DEV_DST_LINEAR)

@@ -10,6 +10,8 @@ import time
 import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "synth"))
+import lz4e_synth  # noqa: E402  (tools/synth: benchmark data generator)
 import bench  # noqa: E402
 
 pkg = importlib.import_module("lz4-sgori_b200")
@@ -46,7 +48,7 @@ def main():
         lay(out_arena, BLOCK, BLOCK)
     mem = src_arena.mem[:nb * BLOCK].reshape(nb, BLOCK)
     for b in range(nb):
-        pkg.lib().lz4e_b200_synth_fill_host(mem[b].ctypes.data, BLOCK, b & 3, b)
+        lz4e_synth.lib().lz4e_synth_fill_host(mem[b].ctypes.data, BLOCK, b & 3, b)
     creqs, keep1 = pkg.make_reqs(src, dst)
     for rep in range(3):
         t0 = time.perf_counter()

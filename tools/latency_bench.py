@@ -10,6 +10,8 @@ import time
 import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "synth"))
+import lz4e_synth  # noqa: E402  (tools/synth: benchmark data generator)
 pkg = importlib.import_module("lz4-sgori_b200")
 NAMES = ["text", "random", "sparse", "mixed"]
 
@@ -19,7 +21,7 @@ def run(ctx, size, cls, n, reps=5):
     stride_d = (bound + 4095) & ~4095
     host = np.zeros((n, size), dtype=np.uint8)
     for b in range(n):
-        pkg.lib().lz4e_b200_synth_fill_host(host[b].ctypes.data, size, cls, 4 * b + cls)
+        lz4e_synth.lib().lz4e_synth_fill_host(host[b].ctypes.data, size, cls, 4 * b + cls)
     d_src, d_dst, d_out = ctx.upload(host), ctx.dev_alloc(n * stride_d), ctx.dev_alloc(n * size)
 
     def tab(base, stride, length):

@@ -10,6 +10,8 @@ import time
 import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "synth"))
+import lz4e_synth  # noqa: E402  (tools/synth: benchmark data generator)
 import bench  # noqa: E402
 
 pkg = importlib.import_module("lz4-sgori_b200")
@@ -25,7 +27,7 @@ def main():
     (sbv, sit), (dbv, dit), (obv, oit) = bench.cfg2_tables(pkg, d_src, d_dst, d_out, n4)
     t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
     r1, r2 = ctx.dev_alloc(4 * n4), ctx.dev_alloc(4 * n4)
-    ctx.synth_fill_dev(t[0], t[1], n4)
+    ctx.sync(); lz4e_synth.dev(0, t[0], t[1], n4, 0, 4096)
     ctx.compress_dev(t[0], t[1], t[2], t[3], n4, 4096, r1, flags=pkg.DEV_DST_LINEAR)
     ctx.sync()
     t0 = time.perf_counter()
@@ -57,7 +59,7 @@ def main():
         obv, oit, _ = bench.cfg3_tables(pkg, c, n64, 65536, 65536, 5)
         t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
         r1, r2 = ctx.dev_alloc(4 * n64), ctx.dev_alloc(4 * n64)
-        ctx.synth_fill_dev(t[0], t[1], n64)
+        ctx.sync(); lz4e_synth.dev(0, t[0], t[1], n64, 0, 65536)
         ctx.compress_dev(t[0], t[1], t[2], t[3], n64, 65536, r1, flags=pkg.DEV_NO_BYU16)
         ctx.sync()
         t0 = time.perf_counter()

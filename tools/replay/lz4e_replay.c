@@ -30,6 +30,7 @@
 #include "lz4e.h"
 #include "lz4e_b200.h"
 #include "lz4e_chunk.h"
+#include "../synth/lz4e_synth.h" /* benchmark data generator (tools/synth) */
 
 struct opts {
 	unsigned qd, batches, min_kib, max_kib, read_pct, seed, capacity_mib, device;
@@ -269,7 +270,7 @@ int main(int argc, char **argv)
 
 					if (piece > bytes - off)
 						piece = bytes - off;
-					lz4e_b200_synth_fill_host((uint8_t *)s->pages + off, piece,
+					lz4e_synth_block((uint8_t *)s->pages + off, piece,
 								  rnd() & 3, rnd());
 					off += piece;
 				}
