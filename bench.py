@@ -352,7 +352,7 @@ def run_ours(args):
         cfg3 = run_cfg3(torch, pkg, ctx, stream, args, dist, rank, world, local)
         if rank == 0:
             result["extra"] = {"cfg3_64k": cfg3}
-    if rank == 0 and world == 1 and not args.no_extra:
+    if rank == 0 and world == 1 and not args.no_extra and not args.no_replay:
         result["extra"]["cfg5_replay"] = run_replay()
     if not args.no_e2e:
         e2e = run_e2e(torch, pkg, ctx, args, dist, rank, world, local)
@@ -767,6 +767,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--no-replay", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-blocks", type=int, default=BLOCKS_PER_GPU)

@@ -83,6 +83,12 @@ void lz4e_b200_ctx_destroy(lz4e_b200_ctx *ctx);
  * message on stderr when no device is usable */
 lz4e_b200_ctx *lz4e_b200_default_ctx(void);
 const char *lz4e_b200_strerror(lz4e_b200_ctx *ctx);
+/* kernel-selection knobs, the same ones the LZ4E_B200_* environment variables
+ * set at context creation (tests and tuning; results never depend on them):
+ * "dgroup" lanes per block of the decoder (1, 4, 8, 16; 0 = automatic),
+ * "dstage" (-1/0/1), "dvariant" (-1 = automatic), "gin_min", "gin_per_sm",
+ * "gin_small".  Returns LZ4E_B200_EINVAL for an unknown key. */
+int lz4e_b200_ctx_tune(lz4e_b200_ctx *ctx, const char *key, int value);
 int lz4e_b200_ctx_device(lz4e_b200_ctx *ctx);
 int lz4e_b200_ctx_sm_count(lz4e_b200_ctx *ctx);
 /* kernels launched by this context so far (bench.py's gpu_launches) */
@@ -106,6 +112,12 @@ int lz4e_b200_sync(lz4e_b200_ctx *ctx, void *stream);
 				     * one contiguous segment (no gather slot
 				     * is reserved for the lane-per-block
 				     * decoder) */
+
+#define LZ4E_B200_DEV_DST_SEGS32 8u /* decompress: no destination has more than
+				     * 32 segments under its iterator, so every
+				     * block is decoded in place through the
+				     * per-block segment map and no linear
+				     * scratch slots are reserved */
 
 /* largest block of one *_dev compress call: 16 MiB.  Up to 64 KiB the hash
  * table holds 16-bit positions; above, 32-bit ones (same number of entries as

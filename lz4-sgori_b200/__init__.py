@@ -27,7 +27,7 @@ REQ = np.dtype([("src", "<u8"), ("dst", "<u8"), ("src_iter", "<u8"), ("dst_iter"
                 ("ret", "<i4"), ("rsvd", "<i4")])
 
 F_SRC_RESIDENT, F_DST_ON_DEVICE, F_KEEP_ITERS, F_DST_PRESERVE = 1, 2, 4, 8
-DEV_NO_BYU16, DEV_DST_LINEAR, DEV_SRC_LINEAR = 1, 2, 4
+DEV_NO_BYU16, DEV_DST_LINEAR, DEV_SRC_LINEAR, DEV_DST_SEGS32 = 1, 2, 4, 8
 
 
 class Lz4eError(RuntimeError):
@@ -64,6 +64,7 @@ def lib():
         "lz4e_b200_ctx_destroy": (None, [vp]),
         "lz4e_b200_default_ctx": (vp, []),
         "lz4e_b200_strerror": (ctypes.c_char_p, [vp]),
+        "lz4e_b200_ctx_tune": (i32, [vp, ctypes.c_char_p, i32]),
         "lz4e_b200_ctx_device": (i32, [vp]),
         "lz4e_b200_ctx_sm_count": (i32, [vp]),
         "lz4e_b200_kernel_launches": (u64, [vp]),
@@ -140,6 +141,9 @@ class Context:
     def check(self, rc, what):
         if rc != 0:
             raise Lz4eError(f"{what} failed with {rc}: {self.err()}")
+
+    def tune(self, key, value):
+        self.check(lib().lz4e_b200_ctx_tune(self.h, key.encode(), int(value)), "tune " + key)
 
     def sync(self, stream=None):
         self.check(lib().lz4e_b200_sync(self.h, _p(stream)), "sync")

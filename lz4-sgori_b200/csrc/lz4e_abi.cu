@@ -38,11 +38,11 @@ struct lz4e_b200_ctx {
 	uint32_t *d_ctl; /* work counters + fault word */
 	std::atomic<uint32_t> ctl_next;
 	std::atomic<uint64_t> launches;
-	uint8_t *scratch;
-	size_t scratch_bytes;
-	/* input slots of the GIN compress kernels, one buffer per stream in use */
+	/* work buffers, one per (stream, purpose) in use: launches on different
+	 * streams never share slots */
 	struct cslot {
 		cudaStream_t stream;
+		int kind; /* SCRATCH_* */
 		uint8_t *p;
 		size_t bytes;
 	};
@@ -54,8 +54,10 @@ struct lz4e_b200_ctx {
 	std::mutex mu;
 	std::vector<lz4e_b200_arena *> arenas;
 	char err[256];
-	int dgroup;  /* decompression group size: 8, 16 or 32 */
+	int dgroup;  /* decompression group size: 1 (lane per block), 4, 8, 16; 0 auto */
 	int dstage;  /* -1 auto, 0 never stage, 1 stage when it fits */
+	int dvariant; /* LZ4E_DV_*: which decoder; -1 auto */
+	int dorder;   /* cost-ordered work queue from this many blocks on; 0 = never */
 };
 
 static void set_err(lz4e_b200_ctx *ctx, const char *fmt, ...)
@@ -125,8 +127,6 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 	ctx->sm_count = prop.multiProcessorCount;
 	ctx->ctl_next = 0;
 	ctx->launches = 0;
-	ctx->scratch = nullptr;
-	ctx->scratch_bytes = 0;
 	ctx->err[0] = 0;
 	ctx->dgroup = 0; /* auto: by block size */
 	ctx->dstage = -1;
@@ -138,6 +138,12 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 	}
 	if (const char *e = getenv("LZ4E_B200_DSTAGE"))
 		ctx->dstage = atoi(e) ? 1 : 0;
+	ctx->dvariant = -1;
+	if (const char *e = getenv("LZ4E_B200_DVARIANT"))
+		ctx->dvariant = atoi(e);
+	ctx->dorder = 2048;
+	if (const char *e = getenv("LZ4E_B200_DORDER"))
+		ctx->dorder = atoi(e);
 	ctx->gin_min = 12288;
 	ctx->gin_per_sm = 0;
 	ctx->gin_small = 2;
@@ -165,7 +171,6 @@ void lz4e_b200_ctx_destroy(lz4e_b200_ctx *ctx)
 		return;
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
-	cudaFree(ctx->scratch);
 	for (auto &c : ctx->cscratch)
 		cudaFree(c.p);
 	cudaFree(ctx->d_ctl);
@@ -191,6 +196,29 @@ lz4e_b200_ctx *lz4e_b200_default_ctx(void)
 const char *lz4e_b200_strerror(lz4e_b200_ctx *ctx)
 {
 	return ctx ? ctx->err : "no context";
+}
+
+int lz4e_b200_ctx_tune(lz4e_b200_ctx *ctx, const char *key, int value)
+{
+	if (!ctx || !key)
+		return LZ4E_B200_EINVAL;
+	if (!strcmp(key, "dgroup"))
+		ctx->dgroup = value;
+	else if (!strcmp(key, "dstage"))
+		ctx->dstage = value;
+	else if (!strcmp(key, "dvariant"))
+		ctx->dvariant = value;
+	else if (!strcmp(key, "dorder"))
+		ctx->dorder = value;
+	else if (!strcmp(key, "gin_min"))
+		ctx->gin_min = value;
+	else if (!strcmp(key, "gin_per_sm"))
+		ctx->gin_per_sm = value;
+	else if (!strcmp(key, "gin_small"))
+		ctx->gin_small = value;
+	else
+		return LZ4E_B200_EINVAL;
+	return LZ4E_B200_OK;
 }
 
 int lz4e_b200_ctx_device(lz4e_b200_ctx *ctx) { return ctx->device; }
@@ -435,30 +463,20 @@ static uint32_t *next_counter(lz4e_b200_ctx *ctx, cudaStream_t s)
 	return c;
 }
 
-static int ensure_scratch(lz4e_b200_ctx *ctx, size_t bytes)
-{
-	if (bytes <= ctx->scratch_bytes)
-		return LZ4E_B200_OK;
-	CU(ctx, cudaDeviceSynchronize());
-	cudaFree(ctx->scratch);
-	ctx->scratch = nullptr;
-	ctx->scratch_bytes = 0;
-	if (cudaMalloc((void **)&ctx->scratch, bytes) != cudaSuccess) {
-		set_err(ctx, "scratch of %zu bytes: out of device memory", bytes);
-		return LZ4E_B200_ENOMEM;
-	}
-	ctx->scratch_bytes = bytes;
-	return LZ4E_B200_OK;
-}
+enum { SCRATCH_COMPRESS_IN = 0, SCRATCH_DECOMPRESS = 1, SCRATCH_COMPACT = 2, SCRATCH_ORDER = 3 };
 
-/* input slots for a GIN compress launch on stream s (kept per stream, so
- * launches on different streams never share slots) */
-static uint8_t *compress_slots(lz4e_b200_ctx *ctx, cudaStream_t s, size_t bytes)
+/*
+ * Work buffer of `bytes` bytes for a launch of the given purpose on stream s.
+ * Buffers are kept per (stream, purpose): two launches on different streams
+ * never share slots, and work already enqueued on s keeps its buffer (growing
+ * waits for the stream first).
+ */
+static uint8_t *stream_scratch(lz4e_b200_ctx *ctx, cudaStream_t s, int kind, size_t bytes)
 {
 	std::lock_guard<std::mutex> lk(ctx->mu);
 
 	for (auto &c : ctx->cscratch) {
-		if (c.stream != s)
+		if (c.stream != s || c.kind != kind)
 			continue;
 		if (c.bytes >= bytes)
 			return c.p;
@@ -474,7 +492,7 @@ static uint8_t *compress_slots(lz4e_b200_ctx *ctx, cudaStream_t s, size_t bytes)
 		c.bytes = bytes;
 		return c.p;
 	}
-	lz4e_b200_ctx::cslot c = { s, nullptr, 0 };
+	lz4e_b200_ctx::cslot c = { s, kind, nullptr, 0 };
 
 	if (cudaMalloc((void **)&c.p, bytes) != cudaSuccess)
 		return nullptr;
@@ -484,9 +502,9 @@ static uint8_t *compress_slots(lz4e_b200_ctx *ctx, cudaStream_t s, size_t bytes)
 }
 
 /* internal helpers for the other translation units */
-uint8_t *lz4e_ctx_scratch(lz4e_b200_ctx *ctx, size_t bytes)
+uint8_t *lz4e_ctx_scratch(lz4e_b200_ctx *ctx, void *stream, size_t bytes)
 {
-	return ensure_scratch(ctx, bytes) == LZ4E_B200_OK ? ctx->scratch : nullptr;
+	return stream_scratch(ctx, pick(ctx, stream), SCRATCH_COMPACT, bytes);
 }
 uint32_t *lz4e_ctx_faults(lz4e_b200_ctx *ctx) { return ctx->d_ctl + CTL_FAULTS; }
 void *lz4e_ctx_stream(lz4e_b200_ctx *ctx, void *stream) { return (void *)pick(ctx, stream); }
@@ -584,7 +602,8 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 				if (grid < 1)
 					grid = 1;
 			}
-			a.in_scratch = compress_slots(ctx, s, (size_t)grid * a.warps * a.in_stride + 256);
+			a.in_scratch = stream_scratch(ctx, s, SCRATCH_COMPRESS_IN,
+						      (size_t)grid * a.warps * a.in_stride + 256);
 			if (!a.in_scratch) {
 				set_err(ctx, "compress input slots (%zu bytes): out of device memory",
 					(size_t)grid * a.in_stride);
@@ -611,41 +630,59 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 {
 	lz4e_decompress_args a;
 	cudaStream_t s;
-	int stage, grid_limit = 0;
-	/*
-	 * lanes per block: 8 for the 4 KiB chunk size, 16 for large blocks in
-	 * small batches (measured on B200: 64 KiB blocks 106 -> 130 GB/s; 4 KiB
-	 * 290 vs 225).
-	 * Small blocks in batches large enough to give every resident lane a
-	 * block of its own go to the lane-per-block decoder ("1"; 4 KiB mixed
-	 * 290 -> 325 GB/s at 262144 blocks, but 140 vs 232 GB/s at 65536).
-	 */
-	int group = (ctx && ctx->dgroup) ? ctx->dgroup : (max_out_bytes > 8192u ? 16 : 8);
-
-	/* large blocks: 8 lanes per block once the batch fills every resident
-	 * group of 8 (64 KiB over 16 segments, 32768 blocks: 150 -> 161 GB/s) */
-	if (ctx && !ctx->dgroup && max_out_bytes > 8192u &&
-	    nblocks >= (uint32_t)ctx->sm_count * 9u * LZ4E_D_WARPS * 4u)
-		group = 8;
-
-	if (ctx && !ctx->dgroup && max_out_bytes <= 8192u &&
-	    nblocks >= (uint32_t)ctx->sm_count * 24u * 32u)
-		group = 1;
+	int stage, grid_limit = 0, group, variant;
+	const bool dst_linear = flags & LZ4E_B200_DEV_DST_LINEAR;
+	const bool small = max_out_bytes <= 8192u;
 
 	if (!ctx)
 		return LZ4E_B200_ENODEV;
 	if (nblocks == 0)
 		return LZ4E_B200_OK;
-	cudaSetDevice(ctx->device);
-	s = pick(ctx, stream);
-	/* small blocks with scattered destinations are built in shared memory and
-	 * flushed segment by segment; linear destinations are decoded in place
-	 * (more resident warps) */
-	stage = max_out_bytes <= 4096u + 64u && !(flags & LZ4E_B200_DEV_DST_LINEAR);
+	/*
+	 * Which decoder (measured on B200, profiles/r2d_decoder_variants.md):
+	 *  - blocks above 8 KiB: the group decoder of lz4e_decompress_group.cuh
+	 *    with pipelined match heads, 16 lanes per block while the batch
+	 *    cannot fill the resident groups of 8 (the serial chain of one
+	 *    block bounds the launch), 8 lanes otherwise;
+	 *  - small blocks, batch large enough to give every resident LANE a
+	 *    block: the lane-per-block decoder;
+	 *  - small blocks otherwise: the group decoder, 8 lanes, output staged in
+	 *    shared memory when the destination is scattered or the batch fits
+	 *    one wave of staged groups, in place otherwise.
+	 * LZ4E_B200_DVARIANT / _DGROUP / _DSTAGE (or lz4e_b200_ctx_tune) override.
+	 */
+	const uint32_t resident8 = (uint32_t)ctx->sm_count * 7u * LZ4E_D_WARPS * 4u;
+	const uint32_t lanes_all = (uint32_t)ctx->sm_count * 24u * 32u;
+	const uint32_t stage_wave = (uint32_t)ctx->sm_count * 3u * LZ4E_D_WARPS * 4u;
+	const bool can_stage = max_out_bytes <= 4096u + 64u;
+
+	if (small && nblocks >= lanes_all) {
+		group = 1;
+		variant = LZ4E_DV_OLD;
+		stage = 0;
+	} else if (small) {
+		group = 8;
+		stage = can_stage && (!dst_linear || nblocks <= stage_wave);
+		variant = stage ? LZ4E_DV_GROUP_PIPE : LZ4E_DV_GROUP;
+	} else {
+		group = nblocks < resident8 ? 16 : 8;
+		variant = LZ4E_DV_GROUP_PIPE;
+		stage = 0;
+	}
+	if (ctx->dvariant >= 0)
+		variant = ctx->dvariant;
+	if (ctx->dgroup)
+		group = ctx->dgroup;
 	if (ctx->dstage == 0)
 		stage = 0;
-	if (ctx->dstage == 1 && max_out_bytes <= 4096u + 64u)
+	if (ctx->dstage == 1 && can_stage)
 		stage = 1;
+	if (group == 1)
+		stage = 0;
+	else if (variant != LZ4E_DV_OLD && group != 4 && group != 8 && group != 16)
+		group = 8;
+	cudaSetDevice(ctx->device);
+	s = pick(ctx, stream);
 	a.src_bvecs = src_bvecs;
 	a.src_iters = src_iters;
 	a.dst_bvecs = dst_bvecs;
@@ -658,12 +695,32 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 	a.scratch_stride = 0;
 	a.in_scratch = nullptr;
 	a.in_stride = 0;
+	a.order = nullptr;
+	if (variant != LZ4E_DV_OLD || group == 1) {
+		/* hand the blocks out by decreasing estimated cost (lz4e_order.cu) */
+		if (ctx->dorder > 0 && nblocks >= (uint32_t)ctx->dorder) {
+			uint32_t *ord = (uint32_t *)stream_scratch(
+				ctx, s, SCRATCH_ORDER,
+				((size_t)nblocks + 2 * LZ4E_ORDER_BUCKETS) * sizeof(uint32_t));
+
+			if (!ord) {
+				set_err(ctx, "decompress work queue: out of device memory");
+				return LZ4E_B200_ENOMEM;
+			}
+			if (lz4e_launch_order(src_iters, dst_iters, nblocks, ord + nblocks, ord, s)) {
+				set_err(ctx, "order launch failed: %s",
+					cudaGetErrorString(cudaGetLastError()));
+				return LZ4E_B200_EIO;
+			}
+			ctx->launches += 2;
+			a.order = ord;
+		}
+	}
 	if (group == 1) {
 		/* lane-per-block decoder: one output slot per resident lane unless
 		 * every destination is contiguous, one input slot unless every
 		 * source is */
-		const uint32_t ostride =
-			(flags & LZ4E_B200_DEV_DST_LINEAR) ? 0u : ((max_out_bytes + 255u) & ~255u);
+		const uint32_t ostride = dst_linear ? 0u : ((max_out_bytes + 255u) & ~255u);
 		const uint32_t istride =
 			(flags & LZ4E_B200_DEV_SRC_LINEAR) ? 0u : ((max_in_bytes + 255u) & ~255u);
 		const size_t per_cta = (size_t)LZ4E_D_WARPS * 32 * ((size_t)ostride + istride);
@@ -671,7 +728,7 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 		stage = 0;
 		a.stage_cap = 0;
 		if (per_cta) {
-			int grid = lz4e_decompress_max_grid(1, 0, 0, ctx->sm_count);
+			int grid = lz4e_decompress_max_grid(1, 0, 0, ctx->sm_count, LZ4E_DV_OLD);
 			const size_t budget = (size_t)6 << 30;
 			const long long want =
 				((long long)nblocks + LZ4E_D_WARPS * 32 - 1) / (LZ4E_D_WARPS * 32);
@@ -688,45 +745,55 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 					grid = 1;
 			}
 			grid_limit = grid;
-			int rc = ensure_scratch(ctx, (size_t)grid * per_cta);
+			uint8_t *scr = stream_scratch(ctx, s, SCRATCH_DECOMPRESS, (size_t)grid * per_cta);
 
-			if (rc)
-				return rc;
+			if (!scr) {
+				set_err(ctx, "decompress scratch: out of device memory");
+				return LZ4E_B200_ENOMEM;
+			}
 			if (ostride) {
-				a.scratch = ctx->scratch;
+				a.scratch = scr;
 				a.scratch_stride = ostride;
 			}
 			if (istride) {
-				a.in_scratch = ctx->scratch +
-					       (size_t)grid * LZ4E_D_WARPS * 32 * ostride;
+				a.in_scratch = scr + (size_t)grid * LZ4E_D_WARPS * 32 * ostride;
 				a.in_stride = istride;
 			}
 		}
-	} else if (!stage && !(flags & LZ4E_B200_DEV_DST_LINEAR)) {		/* one linear slot per resident group for scattered destinations */
+	} else if (!stage && !dst_linear &&
+		   !(variant != LZ4E_DV_OLD && (flags & LZ4E_B200_DEV_DST_SEGS32))) {
+		/* one linear slot per resident group: the round-1 decoder decodes
+		 * every scattered block there; the group decoder only blocks whose
+		 * destination has more segments than its map holds */
 		const uint32_t stride = (max_out_bytes + 255u) & ~255u;
-		int grid = lz4e_decompress_max_grid(group, 0, 0, ctx->sm_count);
+		int grid = lz4e_decompress_max_grid(group, 0, 0, ctx->sm_count, variant);
 		const size_t per_cta = (size_t)LZ4E_D_WARPS * (32 / group) * stride;
 		const size_t budget = (size_t)2 << 30;
+		const long long want = ((long long)nblocks + LZ4E_D_WARPS * (32 / group) - 1) /
+				       (LZ4E_D_WARPS * (32 / group));
 
 		if (grid < 1) {
 			set_err(ctx, "decompress occupancy query failed");
 			return LZ4E_B200_EIO;
 		}
+		if (grid > want)
+			grid = (int)want;
 		if ((size_t)grid * per_cta > budget) {
 			grid = (int)(budget / per_cta);
 			if (grid < 1)
 				grid = 1;
 		}
 		grid_limit = grid;
-		int rc = ensure_scratch(ctx, (size_t)grid * per_cta);
-
-		if (rc)
-			return rc;
-		a.scratch = ctx->scratch;
+		a.scratch = stream_scratch(ctx, s, SCRATCH_DECOMPRESS, (size_t)grid * per_cta);
+		if (!a.scratch) {
+			set_err(ctx, "decompress scratch: out of device memory");
+			return LZ4E_B200_ENOMEM;
+		}
 		a.scratch_stride = stride;
 	}
 	a.work_counter = next_counter(ctx, s);
-	if (lz4e_launch_decompress(&a, group, stage, ctx->sm_count, s, grid_limit, nullptr)) {
+	if (lz4e_launch_decompress(&a, group, stage, variant, ctx->sm_count, s, grid_limit,
+				   nullptr)) {
 		set_err(ctx, "decompress launch failed: %s",
 			cudaGetErrorString(cudaGetLastError()));
 		return LZ4E_B200_EIO;

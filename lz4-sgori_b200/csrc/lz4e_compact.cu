@@ -19,7 +19,7 @@
 #include "lz4e_kernels.h"
 
 extern "C" {
-uint8_t *lz4e_ctx_scratch(lz4e_b200_ctx *ctx, size_t bytes);
+uint8_t *lz4e_ctx_scratch(lz4e_b200_ctx *ctx, void *stream, size_t bytes);
 uint32_t *lz4e_ctx_faults(lz4e_b200_ctx *ctx);
 void *lz4e_ctx_stream(lz4e_b200_ctx *ctx, void *stream);
 void lz4e_ctx_count_launches(lz4e_b200_ctx *ctx, unsigned k);
@@ -150,7 +150,7 @@ extern "C" int lz4e_b200_compress_compact_dev(
 	const size_t bv_bytes = ((size_t)nblocks * sizeof(lz4e_b200_dev_bvec) + 255) & ~(size_t)255;
 	const size_t it_bytes = ((size_t)nblocks * sizeof(lz4e_b200_dev_iter) + 255) & ~(size_t)255;
 	const size_t pf_bytes = (((size_t)dst_nbvecs + 1) * 8 + 255) & ~(size_t)255;
-	uint8_t *scr = lz4e_ctx_scratch(ctx, slot_bytes + bv_bytes + it_bytes + pf_bytes);
+	uint8_t *scr = lz4e_ctx_scratch(ctx, stream, slot_bytes + bv_bytes + it_bytes + pf_bytes);
 
 	if (!scr)
 		return LZ4E_B200_ENOMEM;

@@ -56,6 +56,9 @@ struct lz4e_decompress_args {
 	 * for compressed blocks whose source is not one contiguous segment */
 	uint8_t *in_scratch;
 	uint32_t in_stride;
+	/* work item i is block order[i] (cost-ordered queue, lz4e_order.cu);
+	 * NULL = batch order */
+	const uint32_t *order;
 };
 
 

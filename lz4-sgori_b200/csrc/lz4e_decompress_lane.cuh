@@ -391,7 +391,8 @@ LZ4E_DEV void lz4e_decompress_lanes(const lz4e_decompress_args &a,
 					if (b >= a.nblocks)
 						g.done = true;
 					else
-						lz4e_dlane_open(a, g, b, slot0 + lane);
+						lz4e_dlane_open(a, g, a.order ? a.order[b] : b,
+								slot0 + lane);
 				}
 			}
 		}

@@ -8,6 +8,7 @@
 #include "lz4e_compress_body.cuh"
 #include "lz4e_decompress_body.cuh"
 #include "lz4e_decompress_lane.cuh"
+#include "lz4e_decompress_group.cuh"
 #include "lz4e_kernels.h"
 
 extern __shared__ __align__(16) uint8_t lz4e_smem[];
@@ -36,6 +37,22 @@ lz4e_decompress_kernel(const lz4e_decompress_args a)
 	const uint32_t slot0 = (blockIdx.x * LZ4E_D_WARPS + warp) * groups;
 
 	lz4e_decompress_warp_impl<GS, STAGE>(a, sm, slot0, threadIdx.x & 31);
+}
+
+/* ---- K4G: the group decoder of lz4e_decompress_group.cuh: in-place scattered
+ * output through a per-group segment map (or staged in shared memory), parse
+ * window in registers, pipelined short matches (PIPE) ------------------------ */
+template <int GS, bool STAGE, bool PIPE>
+__global__ void __launch_bounds__(LZ4E_D_WARPS * 32)
+lz4e_decompress_group_kernel(const lz4e_decompress_args a)
+{
+	const uint32_t warp = threadIdx.x >> 5;
+	constexpr uint32_t groups = 32 / GS;
+	const size_t per_group = STAGE ? (size_t)(a.stage_cap + LZ4E_D_PAD) : sizeof(lz4e_omap);
+	uint8_t *sm = lz4e_smem + (size_t)warp * groups * per_group;
+	const uint32_t slot0 = (blockIdx.x * LZ4E_D_WARPS + warp) * groups;
+
+	lz4e_decompress_groups<GS, STAGE, PIPE>(a, sm, slot0, threadIdx.x & 31);
 }
 
 /* ---- K4L: lane-per-block decompression, 32 blocks in flight per warp ------ */
@@ -204,9 +221,93 @@ static int launch_decompress_lanes(const lz4e_decompress_args *a, int sm_count,
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
-int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_count)
+typedef void (*lz4e_dgroup_fn)(const lz4e_decompress_args);
+
+template <bool STAGE, bool PIPE>
+static lz4e_dgroup_fn dgroup_fn_gs(int group)
+{
+	switch (group) {
+	case 4:
+		return lz4e_decompress_group_kernel<4, STAGE, PIPE>;
+	case 16:
+		return lz4e_decompress_group_kernel<16, STAGE, PIPE>;
+	default:
+		return lz4e_decompress_group_kernel<8, STAGE, PIPE>;
+	}
+}
+
+/* variant: LZ4E_DV_GROUP (synchronous copies) or LZ4E_DV_GROUP_PIPE */
+static lz4e_dgroup_fn dgroup_fn(int group, int stage, int variant)
+{
+	const bool pipe = variant == LZ4E_DV_GROUP_PIPE;
+
+	if (stage)
+		return pipe ? dgroup_fn_gs<true, true>(group) : dgroup_fn_gs<true, false>(group);
+	return pipe ? dgroup_fn_gs<false, true>(group) : dgroup_fn_gs<false, false>(group);
+}
+
+static int dgroup_norm(int group)
+{
+	return group == 4 || group == 16 ? group : 8;
+}
+
+static size_t dgroup_smem(int group, int stage, uint32_t stage_cap)
+{
+	const size_t per_group = stage ? (size_t)(stage_cap + LZ4E_D_PAD) : sizeof(lz4e_omap);
+
+	return (size_t)LZ4E_D_WARPS * (32 / group) * per_group;
+}
+
+static int dgroup_per_sm(int group, int stage, uint32_t stage_cap, int variant)
 {
 	int per_sm = 0;
+	lz4e_dgroup_fn fn = dgroup_fn(group, stage, variant);
+	const size_t smem = dgroup_smem(group, stage, stage_cap);
+
+	if (lz4e_set_smem((const void *)fn, smem))
+		return -1;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, LZ4E_D_WARPS * 32, smem) !=
+		    cudaSuccess ||
+	    per_sm < 1)
+		return -1;
+	return per_sm;
+}
+
+static int launch_decompress_group(const lz4e_decompress_args *a, int group, int stage,
+				   int variant, int sm_count, cudaStream_t stream,
+				   int grid_limit, int *grid_out)
+{
+	group = dgroup_norm(group);
+	const int per_sm = dgroup_per_sm(group, stage, a->stage_cap, variant);
+	const int per_cta = LZ4E_D_WARPS * (32 / group);
+
+	if (per_sm < 1)
+		return -1;
+	long long grid = (long long)per_sm * sm_count;
+	const long long want = ((long long)a->nblocks + per_cta - 1) / per_cta;
+
+	if (grid > want)
+		grid = want;
+	if (grid_limit > 0 && grid > grid_limit)
+		grid = grid_limit;
+	if (grid < 1)
+		grid = 1;
+	dgroup_fn(group, stage, variant)<<<(unsigned)grid, LZ4E_D_WARPS * 32,
+					   dgroup_smem(group, stage, a->stage_cap), stream>>>(*a);
+	if (grid_out)
+		*grid_out = (int)grid;
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_count,
+			     int variant)
+{
+	int per_sm = 0;
+
+	if (variant != LZ4E_DV_OLD && group != 1) {
+		per_sm = dgroup_per_sm(dgroup_norm(group), stage, stage_cap, variant);
+		return per_sm < 1 ? -1 : per_sm * sm_count;
+	}
 
 	if (group == 1) {
 		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
@@ -239,11 +340,14 @@ int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_co
 }
 
 int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
-			   int sm_count, cudaStream_t stream, int grid_limit,
+			   int variant, int sm_count, cudaStream_t stream, int grid_limit,
 			   int *grid_out)
 {
 	if (group == 1)
 		return launch_decompress_lanes(a, sm_count, stream, grid_limit, grid_out);
+	if (variant != LZ4E_DV_OLD)
+		return launch_decompress_group(a, group, stage, variant, sm_count, stream,
+					       grid_limit, grid_out);
 	if (stage) {
 		switch (group) {
 		case 8:

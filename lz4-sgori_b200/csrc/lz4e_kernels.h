@@ -16,9 +16,23 @@ int lz4e_compress_plan(lz4e_compress_args *a, int direct, int gin, int sm_count,
 		       int max_per_sm, int *grid_out, size_t *smem_out);
 int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int gin, int grid,
 			 size_t smem, cudaStream_t stream);
-int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_count);
+/* decoder variants: the round-1 group decoder (lz4e_decompress_body.cuh), the
+ * group decoder of lz4e_decompress_group.cuh without / with pipelined matches */
+#define LZ4E_DV_OLD 0
+#define LZ4E_DV_GROUP 1
+#define LZ4E_DV_GROUP_PIPE 2
+
+int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_count,
+			     int variant);
 int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
-			   int sm_count, cudaStream_t stream, int grid_limit,
+			   int variant, int sm_count, cudaStream_t stream, int grid_limit,
 			   int *grid_out);
+
+/* cost-ordered work queue (lz4e_order.cu): order[] receives the block indices
+ * by decreasing estimated decoding cost; ctl = 2 * LZ4E_ORDER_BUCKETS words */
+#define LZ4E_ORDER_BUCKETS 64u
+int lz4e_launch_order(const struct lz4e_b200_dev_iter *src_iters,
+		      const struct lz4e_b200_dev_iter *dst_iters, uint32_t n, uint32_t *ctl,
+		      uint32_t *order, cudaStream_t stream);
 
 #endif

@@ -18,6 +18,9 @@
 #if defined(__CUDACC__)
 
 #define LZ4E_DEV __device__ __forceinline__
+/* rare paths are kept out of line so that the hot loops stay small enough for
+ * the instruction cache */
+#define LZ4E_DEV_NOINLINE __device__ __noinline__
 #define LZ4E_FULL 0xffffffffu
 /* address-space hint for pointers rebuilt from 64-bit descriptor fields */
 #define LZ4E_ASSUME_GLOBAL(p) __builtin_assume(__isGlobal(p))
@@ -56,6 +59,7 @@ LZ4E_DEV uint32_t lz4e_atomic_add(uint32_t *p, uint32_t v)
 }
 LZ4E_DEV void lz4e_atomic_or(uint32_t *p, uint32_t v) { atomicOr(p, v); }
 LZ4E_DEV uint32_t lz4e_min(uint32_t a, uint32_t b) { return a < b ? a : b; }
+LZ4E_DEV float lz4e_rcpf(float x) { return __frcp_rn(x); }
 
 #else /* host build for tests/simt */
 

@@ -25,7 +25,7 @@ def load():
     lib.simt_compress_batch.restype = ctypes.c_int
     lib.simt_compress_batch.argtypes = [vp, vp, vp, vp, u32, u32, u32, u32, vp, vp, vp, u32, u32]
     lib.simt_decompress_batch.restype = ctypes.c_int
-    lib.simt_decompress_batch.argtypes = [vp, vp, vp, vp, u32, u32, u32, vp, vp, vp, u32, u32]
+    lib.simt_decompress_batch.argtypes = [vp, vp, vp, vp, u32, u32, u32, vp, vp, vp, u32, u32, u32]
     return lib
 
 
@@ -61,7 +61,8 @@ def compress(lib, src_layout, dst_layout, in_cap=4096, out_cap=4352, seed=1, tab
     return rets, ends, int(faults[0])
 
 
-def decompress(lib, src_layout, dst_layout, group=8, stage_cap=4096, scratch_stride=0, seed=1):
+def decompress(lib, src_layout, dst_layout, group=8, stage_cap=4096, scratch_stride=0, seed=1,
+               variant=0):
     sbv, sit = to_dev(src_layout)
     dbv, dit = to_dev(dst_layout)
     n = len(sit)
@@ -69,6 +70,6 @@ def decompress(lib, src_layout, dst_layout, group=8, stage_cap=4096, scratch_str
     faults = np.zeros(1, dtype=np.uint32)
     scratch = np.zeros(max(1, (32 // group) * scratch_stride + 64), dtype=np.uint8)
     rc = lib.simt_decompress_batch(_p(sbv), _p(sit), _p(dbv), _p(dit), n, group, stage_cap,
-                                   _p(rets), _p(faults), _p(scratch), scratch_stride, seed)
+                                   _p(rets), _p(faults), _p(scratch), scratch_stride, seed, variant)
     assert rc == 0
     return rets, int(faults[0])

@@ -17,6 +17,7 @@
 #include <stdint.h>
 
 #define LZ4E_DEV static inline __attribute__((always_inline))
+#define LZ4E_DEV_NOINLINE static __attribute__((noinline))
 #define LZ4E_FULL 0xffffffffu
 #define LZ4E_ASSUME_GLOBAL(p) ((void)(p))
 #define LZ4E_ASSUME_SHARED(p) ((void)(p))
@@ -65,5 +66,6 @@ LZ4E_DEV void lz4e_atomic_or(uint32_t *p, uint32_t v)
 	__atomic_fetch_or(p, v, __ATOMIC_RELAXED);
 }
 LZ4E_DEV uint32_t lz4e_min(uint32_t a, uint32_t b) { return a < b ? a : b; }
+LZ4E_DEV float lz4e_rcpf(float x) { return 1.0f / x; }
 
 #endif /* LZ4E_SIMT_HOST_H */

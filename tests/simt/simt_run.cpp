@@ -196,6 +196,7 @@ static void run_warp(const std::function<void(uint32_t)> &body, uint32_t seed)
 #include "lz4e_compress_body.cuh"
 #include "lz4e_decompress_body.cuh"
 #include "lz4e_decompress_lane.cuh"
+#include "lz4e_decompress_group.cuh"
 
 extern "C" {
 
@@ -255,12 +256,13 @@ int simt_decompress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 			  const lz4e_b200_dev_iter *dst_iters, uint32_t nblocks,
 			  uint32_t group, uint32_t stage_cap, int32_t *rets,
 			  uint32_t *faults, uint8_t *scratch, uint32_t scratch_stride,
-			  uint32_t seed)
+			  uint32_t seed, uint32_t variant)
 {
 	lz4e_decompress_args a;
 	uint32_t counter = 0;
 	const uint32_t ngroups = 32 / (group ? group : 1);
-	const uint32_t bytes = ngroups * (stage_cap + LZ4E_D_PAD);
+	const uint32_t bytes = ngroups * (stage_cap + LZ4E_D_PAD) +
+			       ngroups * (uint32_t)sizeof(lz4e_omap);
 	void *smraw = nullptr;
 
 	if (posix_memalign(&smraw, 1024, bytes + 64))
@@ -279,6 +281,7 @@ int simt_decompress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 	a.scratch_stride = scratch_stride;
 	a.in_scratch = nullptr;
 	a.in_stride = 0;
+	a.order = nullptr;
 	uint8_t *sm = (uint8_t *)smraw;
 
 	if (group == 1) {
@@ -292,6 +295,32 @@ int simt_decompress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 		simt::run_warp([&](uint32_t lane) { lz4e_decompress_lanes(a, ls, 0, lane); }, seed);
 		free(ins);
 		free(ls);
+		free(smraw);
+		return 0;
+	}
+
+	if (variant) {
+		/* lz4e_decompress_group.cuh: variant 1 synchronous, 2 pipelined */
+#define RUN_G(GS)                                                                        \
+	simt::run_warp(                                                                  \
+		[&](uint32_t lane) {                                                     \
+			if (stage_cap && variant == 2)                                   \
+				lz4e_decompress_groups<GS, true, true>(a, sm, 0, lane);  \
+			else if (stage_cap)                                              \
+				lz4e_decompress_groups<GS, true, false>(a, sm, 0, lane); \
+			else if (variant == 2)                                           \
+				lz4e_decompress_groups<GS, false, true>(a, sm, 0, lane); \
+			else                                                             \
+				lz4e_decompress_groups<GS, false, false>(a, sm, 0, lane); \
+		},                                                                       \
+		seed)
+		if (group == 4)
+			RUN_G(4);
+		else if (group == 16)
+			RUN_G(16);
+		else
+			RUN_G(8);
+#undef RUN_G
 		free(smraw);
 		return 0;
 	}

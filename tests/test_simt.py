@@ -199,3 +199,142 @@ def test_compress_body_blocks_above_64k(simt, ref_lib, gin):
     for b in range(len(datas)):
         assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
         assert int(ends[b]["src_pos"]) == len(datas[b]) - int(so[b]["bi_size"]), b
+
+
+# ---------------------------------------------------------------------------------------------
+# lz4e_decompress_group.cuh: in-place scattered output through the segment map, parse window,
+# pipelined short matches.  (group, variant, stage): variant 1 = synchronous, 2 = pipelined.
+GROUP_CFGS = [(8, 2, False), (4, 2, False), (16, 2, False), (8, 1, False), (4, 1, False),
+              (8, 2, True), (4, 1, True), (16, 2, True)]
+
+
+def _compress_all(ref_lib, datas):
+    src = _host_layout([sg.segs_single(len(d)) for d in datas], datas)
+    cdst, (sizes, _) = common.oracle_compress(ref_lib, src, [sg.segs_single(sg.compress_bound(len(d)))
+                                                             for d in datas])
+    return [cdst.read_block(b, sizes[b]) for b in range(len(datas))]
+
+
+@pytest.mark.parametrize("group,variant,stage", GROUP_CFGS)
+def test_group_decoder_roundtrip(simt, ref_lib, group, variant, stage):
+    """Valid streams of every class over linear, page-wise, odd and random segmentations on
+    both sides (more than 32 destination segments included: the scratch-slot fallback)."""
+    rng = np.random.default_rng(31 + group + variant)
+    datas = []
+    for b in range(44):
+        n = int(rng.integers(1, 4096 if stage else 20000))
+        datas.append(common.synth(n, b & 3, 700 + b))
+    datas.append(np.zeros(4000 if stage else 30000, np.uint8))
+    datas.append(common.lcg_text(4096 if stage else 24000))
+    comps = _compress_all(ref_lib, datas)
+
+    def dst_spec(i, n):
+        k = i % 5
+        if k == 0:
+            return sg.segs_single(n)
+        if k == 1:
+            return sg.segs_pages(n)
+        if k == 2:
+            return sg.segs_odd(n, 16, i)
+        if k == 3:
+            return sg.segs_random(n, rng, max_segs=24)
+        return sg.segs_random(n, rng, max_segs=80)   # > LZ4E_G_MAXSEG now and then
+    csrc = _host_layout([sg.segs_random(len(c), rng) if i % 3 else sg.segs_single(len(c))
+                         for i, c in enumerate(comps)], comps)
+    out = _host_layout([dst_spec(i, len(d)) for i, d in enumerate(datas)])
+    out.arena.mem[:] = 0xEE
+    rets, faults = emu.decompress(simt, csrc, out, group=group, stage_cap=4112 if stage else 0,
+                                  scratch_stride=30208, variant=variant)
+    assert faults == 0
+    assert np.array_equal(rets, [len(d) for d in datas])
+    for b, d in enumerate(datas):
+        assert np.array_equal(out.read_block(b), d), b
+
+
+@pytest.mark.parametrize("group,variant,stage", GROUP_CFGS[:6])
+def test_group_decoder_malformed_streams(simt, ref_lib, group, variant, stage):
+    """Mutated, truncated and random streams: return values (incl. the -(offset)-1 codes,
+    lz4e_decompress.c:458-459) and the bytes of accepted streams equal the reference decoder's,
+    with linear and with scattered source/destination."""
+    rng = np.random.default_rng(5 + group)
+    base = [common.synth(int(rng.integers(20, 3000)), int(rng.integers(0, 4)), i) for i in range(96)]
+    good = _compress_all(ref_lib, base)
+    comps, caps = [], []
+    for b, d in enumerate(base):
+        c = bytearray(good[b].tobytes())
+        r = rng.random()
+        if r < 0.3 and len(c) > 2:
+            c = c[:int(rng.integers(1, len(c)))]
+        elif r < 0.6:
+            for _ in range(int(rng.integers(1, 4))):
+                c[int(rng.integers(0, len(c)))] = int(rng.integers(0, 256))
+        elif r < 0.75:
+            c += bytes(rng.integers(0, 256, int(rng.integers(1, 20)), dtype=np.uint8))
+        elif r < 0.85:
+            c = bytearray(rng.integers(0, 256, int(rng.integers(1, 200)), dtype=np.uint8).tobytes())
+        comps.append(np.frombuffer(bytes(c), dtype=np.uint8))
+        caps.append(max(0, len(d) + int(rng.integers(-20, 20))) if rng.random() < 0.4 else len(d))
+    ref_rets, ref_outs = common.oracle_decode_linear(ref_lib, comps, caps)
+    assert (ref_rets < 0).sum() > 10 and (ref_rets >= 0).sum() > 10
+    for seg_mode in (0, 1):
+        mk = (lambda n: sg.segs_random(n, rng)) if seg_mode else \
+            (lambda n: dict(sg.segs_single(max(n, 1)), size=n))
+        csrc = _host_layout([mk(len(c)) for c in comps], comps)
+        out = _host_layout([mk(c) for c in caps])
+        rets, faults = emu.decompress(simt, csrc, out, group=group, stage_cap=3200 if stage else 0,
+                                      scratch_stride=16384, variant=variant)
+        assert faults == 0
+        assert np.array_equal(rets, ref_rets)
+        for b in range(len(comps)):
+            if rets[b] > 0:
+                assert np.array_equal(out.read_block(b, rets[b]), ref_outs[b]), b
+
+
+@pytest.mark.parametrize("group,variant", [(8, 2), (4, 2), (16, 1)])
+def test_group_decoder_overlaps_across_segments(simt, ref_lib, group, variant):
+    """Runs and patterns of every period crossing destination segment boundaries (short and
+    long matches whose source lies in the segment before or further back), plus matches at
+    offsets of several segments."""
+    rng = np.random.default_rng(77 + group)
+    datas = []
+    for b in range(24):
+        parts = []
+        while sum(len(p) for p in parts) < 6000:
+            period = int(rng.choice([1, 2, 3, 4, 5, 7, 8, 9, 12, 15, 16, 17, 31, 40, 100]))
+            pat = rng.integers(0, 256, period, dtype=np.uint8)
+            n = int(rng.integers(5, 700))
+            parts.append(np.tile(pat, n // period + 1)[:n])
+            parts.append(rng.integers(0, 256, int(rng.integers(0, 40)), dtype=np.uint8))
+            if len(parts) > 6 and rng.random() < 0.5:   # far back-reference
+                allb = np.concatenate(parts)
+                o = int(rng.integers(0, len(allb) - 4))
+                parts.append(allb[o:o + int(rng.integers(4, 300))].copy())
+        datas.append(np.concatenate(parts))
+    comps = _compress_all(ref_lib, datas)
+    csrc = _host_layout([sg.segs_single(len(c)) for c in comps], comps)
+
+    def tiny_segs(n, b):
+        # many small segments (17..300 bytes) so that nearly every match meets a boundary
+        segs, left = [], n
+        while left > 0:
+            ln = min(left, int(rng.integers(17, 300)))
+            segs.append((int(rng.integers(0, 3000)), ln))
+            left -= ln
+        return {"size": n, "segs": segs[:LZ4E_MAXSEG_TEST] if len(segs) <= LZ4E_MAXSEG_TEST else
+                _merge_tail(segs, LZ4E_MAXSEG_TEST), "skip": 0}
+    out = _host_layout([tiny_segs(len(d), b) for b, d in enumerate(datas)])
+    rets, faults = emu.decompress(simt, csrc, out, group=group, stage_cap=0, scratch_stride=0,
+                                  variant=variant)
+    assert faults == 0
+    assert np.array_equal(rets, [len(d) for d in datas])
+    for b, d in enumerate(datas):
+        assert np.array_equal(out.read_block(b), d), b
+
+
+LZ4E_MAXSEG_TEST = 32
+
+
+def _merge_tail(segs, k):
+    """Keep the first k-1 segments, fold the rest into one (stays within the decoder's map)."""
+    tail = sum(ln for _, ln in segs[k - 1:])
+    return segs[:k - 1] + [(0, tail)]
