@@ -677,7 +677,10 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 		stage = 0;
 	if (ctx->dstage == 1 && can_stage)
 		stage = 1;
-	if (group == 1)
+	if (variant == LZ4E_DV_WAVE) {
+		group = 32; /* one warp per block */
+		stage = 0;
+	} else if (group == 1)
 		stage = 0;
 	else if (variant != LZ4E_DV_OLD && group != 4 && group != 8 && group != 16)
 		group = 8;

@@ -9,6 +9,7 @@
 #include "lz4e_decompress_body.cuh"
 #include "lz4e_decompress_lane.cuh"
 #include "lz4e_decompress_group.cuh"
+#include "lz4e_decompress_wave.cuh"
 #include "lz4e_kernels.h"
 
 extern __shared__ __align__(16) uint8_t lz4e_smem[];
@@ -64,6 +65,17 @@ lz4e_decompress_lane_kernel(const lz4e_decompress_args a)
 	const uint32_t slot0 = (blockIdx.x * LZ4E_D_WARPS + warp) * 32u;
 
 	lz4e_decompress_lanes(a, &sm[warp], slot0, threadIdx.x & 31);
+}
+
+/* ---- K4W: the wave decoder of lz4e_decompress_wave.cuh: one warp per block,
+ * 32 sequences per step ------------------------------------------------------ */
+__global__ void __launch_bounds__(LZ4E_D_WARPS * 32)
+lz4e_decompress_wave_kernel(const lz4e_decompress_args a)
+{
+	__shared__ lz4e_wave_smem sm[LZ4E_D_WARPS];
+	const uint32_t warp = threadIdx.x >> 5;
+
+	lz4e_decompress_wave(a, &sm[warp], blockIdx.x * LZ4E_D_WARPS + warp, threadIdx.x & 31);
 }
 
 /* ------------------------------------------------------------------------- */
@@ -221,6 +233,39 @@ static int launch_decompress_lanes(const lz4e_decompress_args *a, int sm_count,
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
+static int wave_per_sm(void)
+{
+	int per_sm = 0;
+
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+		    &per_sm, lz4e_decompress_wave_kernel, LZ4E_D_WARPS * 32, 0) != cudaSuccess ||
+	    per_sm < 1)
+		return -1;
+	return per_sm;
+}
+
+static int launch_decompress_wave(const lz4e_decompress_args *a, int sm_count,
+				  cudaStream_t stream, int grid_limit, int *grid_out)
+{
+	const int per_sm = wave_per_sm();
+
+	if (per_sm < 1)
+		return -1;
+	long long grid = (long long)per_sm * sm_count;
+	const long long want = ((long long)a->nblocks + LZ4E_D_WARPS - 1) / LZ4E_D_WARPS;
+
+	if (grid > want)
+		grid = want;
+	if (grid_limit > 0 && grid > grid_limit)
+		grid = grid_limit;
+	if (grid < 1)
+		grid = 1;
+	lz4e_decompress_wave_kernel<<<(unsigned)grid, LZ4E_D_WARPS * 32, 0, stream>>>(*a);
+	if (grid_out)
+		*grid_out = (int)grid;
+	return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
 typedef void (*lz4e_dgroup_fn)(const lz4e_decompress_args);
 
 template <bool STAGE, bool PIPE>
@@ -304,6 +349,10 @@ int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_co
 {
 	int per_sm = 0;
 
+	if (variant == LZ4E_DV_WAVE) {
+		per_sm = wave_per_sm();
+		return per_sm < 1 ? -1 : per_sm * sm_count;
+	}
 	if (variant != LZ4E_DV_OLD && group != 1) {
 		per_sm = dgroup_per_sm(dgroup_norm(group), stage, stage_cap, variant);
 		return per_sm < 1 ? -1 : per_sm * sm_count;
@@ -343,6 +392,8 @@ int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
 			   int variant, int sm_count, cudaStream_t stream, int grid_limit,
 			   int *grid_out)
 {
+	if (variant == LZ4E_DV_WAVE)
+		return launch_decompress_wave(a, sm_count, stream, grid_limit, grid_out);
 	if (group == 1)
 		return launch_decompress_lanes(a, sm_count, stream, grid_limit, grid_out);
 	if (variant != LZ4E_DV_OLD)

@@ -21,6 +21,7 @@ int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int gin, int g
 #define LZ4E_DV_OLD 0
 #define LZ4E_DV_GROUP 1
 #define LZ4E_DV_GROUP_PIPE 2
+#define LZ4E_DV_WAVE 3 /* lz4e_decompress_wave.cuh: one warp per block */
 
 int lz4e_decompress_max_grid(int group, int stage, uint32_t stage_cap, int sm_count,
 			     int variant);

@@ -197,6 +197,7 @@ static void run_warp(const std::function<void(uint32_t)> &body, uint32_t seed)
 #include "lz4e_decompress_body.cuh"
 #include "lz4e_decompress_lane.cuh"
 #include "lz4e_decompress_group.cuh"
+#include "lz4e_decompress_wave.cuh"
 
 extern "C" {
 
@@ -295,6 +296,20 @@ int simt_decompress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 		simt::run_warp([&](uint32_t lane) { lz4e_decompress_lanes(a, ls, 0, lane); }, seed);
 		free(ins);
 		free(ls);
+		free(smraw);
+		return 0;
+	}
+
+	if (variant == 3) {
+		/* lz4e_decompress_wave.cuh: one warp per block; `scratch` holds one
+		 * output slot */
+		lz4e_wave_smem *wsm = nullptr;
+
+		if (posix_memalign((void **)&wsm, 64, sizeof(*wsm)))
+			return -1;
+		memset(wsm, 0xCD, sizeof(*wsm));
+		simt::run_warp([&](uint32_t lane) { lz4e_decompress_wave(a, wsm, 0, lane); }, seed);
+		free(wsm);
 		free(smraw);
 		return 0;
 	}

@@ -204,8 +204,9 @@ def test_compress_body_blocks_above_64k(simt, ref_lib, gin):
 # ---------------------------------------------------------------------------------------------
 # lz4e_decompress_group.cuh: in-place scattered output through the segment map, parse window,
 # pipelined short matches.  (group, variant, stage): variant 1 = synchronous, 2 = pipelined.
-GROUP_CFGS = [(8, 2, False), (4, 2, False), (16, 2, False), (8, 1, False), (4, 1, False),
-              (8, 2, True), (4, 1, True), (16, 2, True)]
+# (32, 3, False) = the wave decoder (lz4e_decompress_wave.cuh): one warp per block.
+GROUP_CFGS = [(32, 3, False), (8, 2, False), (4, 2, False), (16, 2, False), (8, 1, False),
+              (4, 1, False), (8, 2, True), (4, 1, True), (16, 2, True)]
 
 
 def _compress_all(ref_lib, datas):
@@ -251,7 +252,7 @@ def test_group_decoder_roundtrip(simt, ref_lib, group, variant, stage):
         assert np.array_equal(out.read_block(b), d), b
 
 
-@pytest.mark.parametrize("group,variant,stage", GROUP_CFGS[:6])
+@pytest.mark.parametrize("group,variant,stage", GROUP_CFGS[:7])
 def test_group_decoder_malformed_streams(simt, ref_lib, group, variant, stage):
     """Mutated, truncated and random streams: return values (incl. the -(offset)-1 codes,
     lz4e_decompress.c:458-459) and the bytes of accepted streams equal the reference decoder's,
@@ -290,7 +291,7 @@ def test_group_decoder_malformed_streams(simt, ref_lib, group, variant, stage):
                 assert np.array_equal(out.read_block(b, rets[b]), ref_outs[b]), b
 
 
-@pytest.mark.parametrize("group,variant", [(8, 2), (4, 2), (16, 1)])
+@pytest.mark.parametrize("group,variant", [(32, 3), (8, 2), (4, 2), (16, 1)])
 def test_group_decoder_overlaps_across_segments(simt, ref_lib, group, variant):
     """Runs and patterns of every period crossing destination segment boundaries (short and
     long matches whose source lies in the segment before or further back), plus matches at

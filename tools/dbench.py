@@ -85,7 +85,7 @@ def main():
             return bool(np.array_equal(src_h, ctx.download(d_out, np.uint8, len(src_h))))
         lin = pkg.DEV_DST_LINEAR | pkg.DEV_SRC_LINEAR
         run("4k-linear", n4, 4096, t, d_cit, rets, lin, d_src, chk,
-            [(0, 1, -1, 0), (0, 1, -1, 1), (0, 8, 0, 0), (2, 8, 0, 0), (2, 8, 0, 1), (2, 4, 0, 1),
+            [(3, 32, 0, 0), (3, 32, 0, 1), (0, 1, -1, 0), (0, 1, -1, 1), (0, 8, 0, 0), (2, 8, 0, 0), (2, 8, 0, 1), (2, 4, 0, 1),
              (2, 16, 0, 1), (1, 8, 0, 1), (1, 4, 0, 1), (2, 8, 1, 1), (2, 4, 1, 1)])
         for p in (d_src, d_dst, d_out, r1, d_cit, *t):
             ctx.dev_free(p)
@@ -114,7 +114,7 @@ def main():
         def chk64():
             return all(np.array_equal(w, bench._gather_dev(ctx, obv, oit, i, S)) for w, i in zip(want, sample))
         run("64k-sg16", n64, S, t, d_cit, rets, pkg.DEV_DST_SEGS32, a, chk64,
-            [(0, 8, 0, 0), (2, 8, 0, 0), (2, 8, 0, 1), (2, 4, 0, 1), (2, 16, 0, 1), (1, 8, 0, 1),
+            [(3, 32, 0, 0), (3, 32, 0, 1), (0, 8, 0, 0), (2, 8, 0, 0), (2, 8, 0, 1), (2, 4, 0, 1), (2, 16, 0, 1), (1, 8, 0, 1),
              (1, 4, 0, 1)])
     ctx.close()
 
