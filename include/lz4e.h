@@ -40,6 +40,28 @@ extern "C" {
 		 ? 0                                                        \
 		 : (isize) + ((isize) / 255) + 16)
 
+/*
+ * ref lz4e.h:30-45: the stream state a caller may allocate instead of a raw
+ * LZ4E_MEM_COMPRESS buffer.  Kept so that code declaring an LZ4E_stream_t (or
+ * sizing wrkmem with sizeof) compiles and gets the same 17 440 bytes; this
+ * library never reads the fields (per-bvec sizes and the hash table live in
+ * device tables / shared memory), it only clears the buffer like
+ * lz4e_compress.c:548 does.
+ */
+typedef struct {
+	uint32_t bvIterSize[BIO_MAX_VECS];
+	uint32_t hashTable[LZ4E_HASH_SIZE_U32];
+	uint32_t currentOffset;
+	uint32_t initCheck;
+	const uint8_t *dictionary;
+	uint8_t *bufferStart;
+	uint32_t dictSize;
+} LZ4E_stream_t_internal;
+typedef union {
+	unsigned long long table[LZ4E_STREAMSIZE_U64];
+	LZ4E_stream_t_internal internal_donotuse;
+} LZ4E_stream_t;
+
 /* ref lz4e.h:53-55 */
 #ifndef LZ4E_DISTANCE_MAX
 #define LZ4E_DISTANCE_MAX 65535
@@ -59,6 +81,15 @@ extern "C" {
  *             output capacity too small).  On success the iterators are left
  *             where the reference leaves them: *srcIter at the last match-search
  *             position, *dstIter at the first byte of the final literal run.
+ *             On a 0 return the reference leaves both iterators somewhere in
+ *             the middle of the block and a partial prefix in dst
+ *             (lz4e_compress.c:358-363, :425-430, :509 return from inside the
+ *             loop).  Here a 0 return leaves *srcIter / *dstIter UNCHANGED and
+ *             the destination bytes unspecified (some prefix may have been
+ *             written, never beyond dstIter->bi_size).  That is safe for the
+ *             reference's only caller: lz4e_chunk_compress_ext works on copies
+ *             of the iterators and discards them and the buffer on failure
+ *             (lz4e_bdev/lz4e_chunk.c:143-155).
  */
 int LZ4E_compress_default(const struct bio_vec *src, struct bio_vec *dst,
 			  struct bvec_iter *srcIter, struct bvec_iter *dstIter,

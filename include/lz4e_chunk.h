@@ -64,9 +64,13 @@ void lz4e_chunk_teardown(void);
 void lz4e_buf_copy_from_bio(struct lz4e_buffer *dst, struct bio *src);
 struct lz4e_chunk *lz4e_chunk_alloc(int src_size);
 void lz4e_chunk_free(struct lz4e_chunk *chunk);
-/* src_buf.data -> dst_buf.data, contiguous (the reference calls the kernel's
- * stock LZ4_compress_default here; this build uses the LZ4E codec on a
- * one-segment description of the two buffers) */
+/* src_buf.data -> dst_buf.data, contiguous.  NOTE: the reference calls the
+ * kernel's stock LZ4_compress_default here (lz4e_bdev/lz4e_chunk.c:106-107);
+ * this build runs the LZ4E codec on a one-segment (multi-page bvec, byU32)
+ * description of the two buffers.  Both emit valid LZ4 blocks that either
+ * decoder accepts, but the BYTES differ from the reference's for buffers above
+ * 4 KiB (different hash-table mode); only round trips are guaranteed here.
+ * Byte identity holds for lz4e_chunk_compress_ext, the LZ4E path. */
 int lz4e_chunk_compress(struct lz4e_chunk *chunk);
 /* dst_buf.data -> src_buf.data; the decoded size must equal src_buf.buf_size */
 int lz4e_chunk_decompress(struct lz4e_chunk *chunk);
@@ -115,6 +119,12 @@ void lz4e_dev_stats(struct lz4e_dev *dev, int write, struct lz4e_stats *out);
 void lz4e_dev_stats_reset(struct lz4e_dev *dev);
 /* bytes the codec produced for the writes so far (compressed size) */
 uint64_t lz4e_dev_compressed_bytes(struct lz4e_dev *dev);
+/* order-independent digest of WHAT the codec produced: the wrapping sum, over
+ * all successful writes so far, of lz4e_fnv1a64() of each bio's compressed
+ * bytes — lets a harness compare the bytes of every bio with the reference's
+ * without keeping them */
+uint64_t lz4e_dev_compressed_digest(struct lz4e_dev *dev);
+uint64_t lz4e_fnv1a64(const void *p, size_t n);
 
 #ifdef __cplusplus
 }

@@ -436,6 +436,7 @@ struct lz4e_dev {
 	uint64_t capacity;
 	struct lz4e_stats read_stats, write_stats;
 	uint64_t compressed_bytes;
+	uint64_t compressed_digest; /* sum of FNV-1a-64 over each bio's compressed bytes */
 	pthread_mutex_t mu;
 };
 
@@ -490,12 +491,29 @@ void lz4e_dev_stats_reset(struct lz4e_dev *dev)
 	memset(&dev->read_stats, 0, sizeof(dev->read_stats));
 	memset(&dev->write_stats, 0, sizeof(dev->write_stats));
 	dev->compressed_bytes = 0;
+	dev->compressed_digest = 0;
 	pthread_mutex_unlock(&dev->mu);
 }
 
 uint64_t lz4e_dev_compressed_bytes(struct lz4e_dev *dev)
 {
 	return dev->compressed_bytes;
+}
+
+uint64_t lz4e_dev_compressed_digest(struct lz4e_dev *dev)
+{
+	return dev->compressed_digest;
+}
+
+uint64_t lz4e_fnv1a64(const void *p, size_t n)
+{
+	const uint8_t *b = p;
+	uint64_t h = 1469598103934665603ull;
+	size_t i;
+
+	for (i = 0; i < n; i++)
+		h = (h ^ b[i]) * 1099511628211ull;
+	return h;
 }
 
 /* lz4e_bio_bytes_to_pages, lz4e_req.c:77-82 */
@@ -588,6 +606,8 @@ int lz4e_dev_submit_writes(struct lz4e_dev *dev, struct bio **bios, size_t n, in
 		memcpy(dev->store + (uint64_t)ob->bi_iter.bi_sector * 512u, c->src_buf.data,
 		       (size_t)c->src_buf.data_size);
 		dev->compressed_bytes += (uint64_t)c->dst_buf.data_size;
+		dev->compressed_digest +=
+			lz4e_fnv1a64(c->dst_buf.data, (size_t)c->dst_buf.data_size);
 	}
 	for (i = 0; i < n; i++)
 		stats_update(&dev->write_stats, status[i] != 0,

@@ -46,6 +46,19 @@ def test_sizing_macros_match_reference():
     assert out == ["17440", "4128", "65809", "0", "16", "20"]
 
 
+def test_stream_typedefs_match_reference():
+    """lz4e.h:30-45 of the reference: LZ4E_stream_t / LZ4E_stream_t_internal exist, the union is
+    LZ4E_MEM_COMPRESS bytes and the fields sit where the reference puts them."""
+    src = ('#include <stdio.h>\n#include <stddef.h>\n#include "lz4e.h"\nint main(void){LZ4E_stream_t s;'
+           'printf("%zu %zu %zu %zu %zu\\n", sizeof(s), sizeof(s.table)/sizeof(s.table[0]),'
+           'offsetof(LZ4E_stream_t_internal, hashTable), offsetof(LZ4E_stream_t_internal, currentOffset),'
+           'sizeof(s.internal_donotuse.hashTable));return 0;}')
+    exe = "/tmp/lz4e_stream_probe"
+    subprocess.run(["gcc", "-x", "c", "-", "-I", INCLUDE, "-o", exe], input=src.encode(), check=True)
+    out = subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split()
+    assert out == ["17440", "2180", "1024", "17408", "16384"]
+
+
 def test_no_cpu_fallback_without_device(pkg):
     import torch
     if torch.cuda.is_available():

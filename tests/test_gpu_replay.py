@@ -36,6 +36,8 @@ def test_replay_4k_to_128k(bios):
     r = _run("--qd", "64", "--batches", "6", "--capacity-mib", "64", "--seed", "3", *bios)
     assert r["failed"] == 0 and r["mismatches"] == 0
     assert r["compressed_bytes"] == r["oracle_compressed_bytes"] > 0
+    assert r["per_bio_digest_equal"] is True
+    assert r["per_bio_digest_equal"] is True  # the BYTES of every bio, not just the total
     assert r["gpu_launches"] >= 12  # a compress and a decompress launch per write batch
     assert r["read_reqs"] > 0 and r["write_reqs"] > 0
 
@@ -46,3 +48,4 @@ def test_replay_chunk_size_only():
              "--capacity-mib", "1", "--read-pct", "50", "--seed", "9")
     assert r["failed"] == 0 and r["mismatches"] == 0
     assert r["compressed_bytes"] == r["oracle_compressed_bytes"] > 0
+    assert r["per_bio_digest_equal"] is True

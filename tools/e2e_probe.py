@@ -46,9 +46,7 @@ def main():
         return sg.Layout(arena, bv, idx.copy(), it, arena.npages)
     src, dst, out = lay(src_arena, BLOCK, BLOCK), lay(dst_arena, DST_STRIDE, bound), \
         lay(out_arena, BLOCK, BLOCK)
-    mem = src_arena.mem[:nb * BLOCK].reshape(nb, BLOCK)
-    for b in range(nb):
-        lz4e_synth.lib().lz4e_synth_fill_host(mem[b].ctypes.data, BLOCK, b & 3, b)
+    lz4e_synth.host_blocks(src_arena.mem, BLOCK, BLOCK, nb, first=0)
     creqs, keep1 = pkg.make_reqs(src, dst)
     for rep in range(3):
         t0 = time.perf_counter()

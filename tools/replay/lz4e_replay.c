@@ -174,7 +174,7 @@ int main(int argc, char **argv)
 	uint8_t *shadow, *pages_mem = NULL;
 	double *lat, t_all = 0.0;
 	uint64_t capacity, wbytes = 0, rbytes = 0, wreqs = 0, rreqs = 0, wvecs = 0, rvecs = 0;
-	uint64_t oracle_bytes = 0, launches0;
+	uint64_t oracle_bytes = 0, oracle_digest = 0, launches0;
 	unsigned int max_pages, b, i, bad = 0, failed = 0;
 	ref_compress_fn ref_compress = NULL;
 	void *ref_wrk = NULL;
@@ -287,6 +287,8 @@ int main(int argc, char **argv)
 
 					if (r <= 0)
 						bad++;
+					else
+						oracle_digest += lz4e_fnv1a64(dp, (size_t)r);
 					oracle_bytes += (uint64_t)r;
 					free(dp);
 				}
@@ -333,6 +335,14 @@ int main(int argc, char **argv)
 			(unsigned long long)rs.reqs_total, (unsigned long long)rreqs);
 		bad++;
 	}
+	if (ref_compress && !failed && oracle_digest != lz4e_dev_compressed_digest(dev)) {
+		/* per-bio BYTES: the sum of per-bio FNV-1a-64 digests must agree */
+		fprintf(stderr, "lz4e_replay: compressed bytes differ from the reference's "
+				"(digest %016llx vs %016llx)\n",
+			(unsigned long long)lz4e_dev_compressed_digest(dev),
+			(unsigned long long)oracle_digest);
+		bad++;
+	}
 	if (ref_compress && oracle_bytes != lz4e_dev_compressed_bytes(dev)) {
 		fprintf(stderr, "lz4e_replay: compressed %llu bytes, the reference %llu\n",
 			(unsigned long long)lz4e_dev_compressed_bytes(dev),
@@ -349,14 +359,17 @@ int main(int argc, char **argv)
 		       "%s bio pages\", \"gbs\": %.3f, \"write_gbs\": %.3f, \"batch_ms_p50\": %.3f, "
 		       "\"batch_ms_p99\": %.3f, \"batch_ms_max\": %.3f, \"write_reqs\": %llu, "
 		       "\"read_reqs\": %llu, \"write_bytes\": %llu, \"read_bytes\": %llu, "
-		       "\"compressed_bytes\": %llu, \"oracle_compressed_bytes\": %s%llu, "
+		       "\"compressed_bytes\": %llu, \"oracle_compressed_bytes\": %s%llu, \"per_bio_digest_equal\": %s, "
 		       "\"failed\": %u, \"mismatches\": %u, \"gpu_launches\": %llu%s\n",
 		       "{", o.qd, o.batches, o.min_kib, o.max_kib, o.read_pct,
 		       o.arena_bios ? "arena (pinned, mirrored)" : "pageable (bounced)", gbs, wgbs,
 		       pct(lat, o.batches, 0.50), pct(lat, o.batches, 0.99), lat[o.batches - 1],
 		       (unsigned long long)wreqs, (unsigned long long)rreqs,
 		       (unsigned long long)wbytes, (unsigned long long)rbytes,
-		       (unsigned long long)cbytes, "", (unsigned long long)oracle_bytes, failed, bad,
+		       (unsigned long long)cbytes, "", (unsigned long long)oracle_bytes,
+		       !ref_compress ? "null"
+		       : oracle_digest == lz4e_dev_compressed_digest(dev) ? "true" : "false",
+		       failed, bad,
 		       (unsigned long long)(lz4e_b200_kernel_launches(ctx) - launches0), "}");
 	}
 	for (i = 0; i < o.qd; i++)
