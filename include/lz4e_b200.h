@@ -78,6 +78,9 @@ struct lz4e_b200_dev_end {
 /* ---- context ------------------------------------------------------------- */
 int lz4e_b200_device_count(void);
 int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out);
+/* waits for the device, releases the per-context host workspace and chunk
+ * pool, and destroys every arena still registered with the context (their
+ * handles are invalid afterwards) */
 void lz4e_b200_ctx_destroy(lz4e_b200_ctx *ctx);
 /* process-wide default context on $LZ4E_B200_DEVICE (default 0); NULL and a
  * message on stderr when no device is usable */
@@ -193,12 +196,35 @@ int lz4e_b200_copy_h2d(lz4e_b200_ctx *ctx, void *stream, void *dst_dev,
 int lz4e_b200_copy_d2h(lz4e_b200_ctx *ctx, void *stream, void *dst_host,
 		       const void *src_dev, size_t bytes);
 
+/*
+ * Exact-byte transfers between arena host pages and their device mirror, done
+ * by a kernel over PCIe instead of the copy engines: for block b the first
+ * lens[b] bytes (lens == NULL: iters[b].bi_size bytes; lens[b] <= 0: none) of
+ * the segment list (bvecs, iters[b]) — DEVICE addresses inside arenas of this
+ * context — are copied device -> host (to_host != 0) or host -> device.
+ * Segments that lie in no arena are skipped.  Nothing outside those bytes is
+ * written on either side.  The host batches use it to bring back only the
+ * bytes a compressor produced and to send up only the bytes a decompressor
+ * will read.
+ */
+int lz4e_b200_xfer_dev(lz4e_b200_ctx *ctx, void *stream,
+		       const struct lz4e_b200_dev_bvec *bvecs,
+		       const struct lz4e_b200_dev_iter *iters, const int32_t *lens,
+		       uint32_t nblocks, int to_host);
+/* bytes moved host -> device and device -> host through this context so far
+ * (copy-engine copies enqueued + transfer-kernel bytes completed); waits for
+ * nothing but reads a device counter, so call it after lz4e_b200_sync() */
+int lz4e_b200_traffic(lz4e_b200_ctx *ctx, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
+
 /* streams and events for callers that pipeline *_dev calls with copies (the
  * host-level batches do): opaque cudaStream_t / cudaEvent_t handles */
 void *lz4e_b200_stream_create(lz4e_b200_ctx *ctx);
 void lz4e_b200_stream_destroy(lz4e_b200_ctx *ctx, void *stream);
 void *lz4e_b200_event_create(lz4e_b200_ctx *ctx);
 void lz4e_b200_event_destroy(lz4e_b200_ctx *ctx, void *event);
+/* an event that keeps a timestamp, and the time between two completed ones */
+void *lz4e_b200_event_create_timed(lz4e_b200_ctx *ctx);
+float lz4e_b200_event_elapsed_ms(lz4e_b200_ctx *ctx, void *from, void *to);
 int lz4e_b200_event_record(lz4e_b200_ctx *ctx, void *event, void *stream);
 /* work enqueued on `stream` after this call waits for `event` */
 int lz4e_b200_stream_wait_event(lz4e_b200_ctx *ctx, void *stream, void *event);
@@ -237,15 +263,34 @@ struct lz4e_b200_req {
 #define LZ4E_B200_F_SRC_RESIDENT 1u /* source pages already current on device */
 #define LZ4E_B200_F_DST_ON_DEVICE 2u /* leave results in the device mirror */
 #define LZ4E_B200_F_KEEP_ITERS 4u   /* do not move the iterators */
-/* Destination pages that live in an arena come back with ONE bulk copy of the
- * touched byte range [first, last] of that arena, so host bytes inside that
- * range which the kernels did not write are replaced by the device mirror's.
- * With DST_PRESERVE the range is uploaded first, which keeps every unwritten
- * byte exactly as it was (what a lone LZ4E_compress_default call does). */
+/* No host byte other than the ones the codec produced may change (what a lone
+ * LZ4E_compress_default call guarantees).  Compressed output always comes back
+ * that way (rets[b] bytes per block through the transfer kernel); with this
+ * flag a decompressor's output does too, instead of one copy-engine transfer
+ * of the (densely tiled) destination range. */
 #define LZ4E_B200_F_DST_PRESERVE 8u
 
-/* Pages may live in an arena (fast path: one bulk copy per arena per
- * direction) or anywhere in host memory (bounced segment by segment). */
+/*
+ * How pages travel (host/lz4e_host.c; measured split in
+ * profiles/r2k_e2e_timeline.md):
+ *  - pages in an arena, side tiles the byte range it spans (uncompressed
+ *    blocks end to end): one copy-engine transfer of that range per chunk;
+ *  - compressed output: exactly rets[b] bytes per block, written to the host
+ *    pages by lz4e_xfer_kernel — never the LZ4E_COMPRESSBOUND slot;
+ *  - sources that do NOT tile their range (compressed blocks sitting in their
+ *    slots, scattered segments): the spanned range by copy engine when it is
+ *    at least a quarter full, else exactly the bytes by the transfer kernel.
+ *    The range copy refreshes the device mirror of the bytes IN BETWEEN from
+ *    host memory; a caller that keeps device-only results
+ *    (LZ4E_B200_F_DST_ON_DEVICE) in the same arena must not interleave them
+ *    with another batch's sources, or sets LZ4E_B200_SPARSE_SRC=kernel;
+ *  - pages anywhere else in host memory: packed into pinned staging by the
+ *    context's host threads (sources) / copied back per segment (results).
+ * A batch is cut into chunks that are pipelined over three streams; batches on
+ * different contexts run concurrently, batches on one context take turns.
+ * LZ4E_B200_TRACE=1 prints the host-side split per batch, =2 a device
+ * timeline per chunk.
+ */
 int lz4e_b200_compress_batch(lz4e_b200_ctx *ctx, struct lz4e_b200_req *reqs,
 			     size_t n, unsigned flags);
 int lz4e_b200_decompress_batch(lz4e_b200_ctx *ctx, struct lz4e_b200_req *reqs,

@@ -79,6 +79,8 @@ def lib():
         "lz4e_b200_host_free": (None, [vp, vp]),
         "lz4e_b200_copy_h2d": (i32, [vp, vp, vp, vp, sz]),
         "lz4e_b200_copy_d2h": (i32, [vp, vp, vp, vp, sz]),
+        "lz4e_b200_xfer_dev": (i32, [vp, vp, vp, vp, vp, u32, i32]),
+        "lz4e_b200_traffic": (i32, [vp, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
         "lz4e_b200_arena_create": (i32, [vp, sz, ctypes.POINTER(vp)]),
         "lz4e_b200_arena_destroy": (None, [vp]),
         "lz4e_b200_arena_pages": (vp, [vp]),
@@ -195,6 +197,16 @@ class Context:
         self.check(lib().lz4e_b200_compress_compact_dev(
             self.h, _p(stream), _p(sbv), _p(sit), _p(dbv), dst_nbvecs, dst_done, dst_cap, nblocks,
             max_in, flags, _p(rets), _p(offsets)), "compress_compact_dev")
+
+    def xfer_dev(self, bv, it, lens, nblocks, to_host, stream=None):
+        self.check(lib().lz4e_b200_xfer_dev(self.h, _p(stream), _p(bv), _p(it), _p(lens), nblocks,
+                                            1 if to_host else 0), "xfer_dev")
+
+    def traffic(self):
+        """(h2d bytes, d2h bytes) moved through this context so far."""
+        a, b = ctypes.c_uint64(), ctypes.c_uint64()
+        self.check(lib().lz4e_b200_traffic(self.h, ctypes.byref(a), ctypes.byref(b)), "traffic")
+        return a.value, b.value
 
     # ---- host-level calls ----
     def compress_batch(self, reqs, flags=0):

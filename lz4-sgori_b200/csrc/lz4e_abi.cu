@@ -59,6 +59,18 @@ struct lz4e_b200_ctx {
 	int dvariant; /* LZ4E_DV_*: which decoder; -1 auto */
 	int dorder;   /* cost-ordered work queue from this many blocks on; 0 = never */
 	int wave_min; /* blocks above 8 KiB: wave decoder from this many blocks on */
+	/* bytes moved between host and device through this context: copy engine
+	 * (host counters) and lz4e_xfer_kernel (device counters d_moved[0..1]) */
+	std::atomic<uint64_t> h2d_bytes, d2h_bytes;
+	unsigned long long *d_moved;
+	/* state other layers hang on the context (host workspace, chunk pool):
+	 * created once, torn down by lz4e_b200_ctx_destroy */
+	struct attachment {
+		int slot;
+		void *p;
+		void (*dtor)(lz4e_b200_ctx *, void *);
+	};
+	std::vector<attachment> attached;
 };
 
 static void set_err(lz4e_b200_ctx *ctx, const char *fmt, ...)
@@ -157,9 +169,14 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 		ctx->gin_min = atoi(e);
 	if (const char *e = getenv("LZ4E_B200_GIN_PER_SM"))
 		ctx->gin_per_sm = atoi(e);
+	ctx->h2d_bytes = 0;
+	ctx->d2h_bytes = 0;
+	ctx->d_moved = nullptr;
 	if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
 	    cudaMalloc((void **)&ctx->d_ctl, CTL_WORDS * sizeof(uint32_t)) != cudaSuccess ||
-	    cudaMemset(ctx->d_ctl, 0, CTL_WORDS * sizeof(uint32_t)) != cudaSuccess) {
+	    cudaMemset(ctx->d_ctl, 0, CTL_WORDS * sizeof(uint32_t)) != cudaSuccess ||
+	    cudaMalloc((void **)&ctx->d_moved, 2 * sizeof(unsigned long long)) != cudaSuccess ||
+	    cudaMemset(ctx->d_moved, 0, 2 * sizeof(unsigned long long)) != cudaSuccess) {
 		fprintf(stderr, "lz4e_b200: context setup failed: %s\n",
 			cudaGetErrorString(cudaGetLastError()));
 		delete ctx;
@@ -174,10 +191,24 @@ void lz4e_b200_ctx_destroy(lz4e_b200_ctx *ctx)
 	if (!ctx)
 		return;
 	cudaSetDevice(ctx->device);
-	cudaStreamSynchronize(ctx->stream);
+	cudaDeviceSynchronize();
+	/* layers above first (they may still own arenas and streams), newest first */
+	while (!ctx->attached.empty()) {
+		lz4e_b200_ctx::attachment at = ctx->attached.back();
+
+		ctx->attached.pop_back();
+		if (at.dtor)
+			at.dtor(ctx, at.p);
+		free(at.p);
+	}
+	/* arenas the caller left behind go with the context: their handles are
+	 * invalid from here on (documented in lz4e_b200.h) */
+	while (!ctx->arenas.empty())
+		lz4e_b200_arena_destroy(ctx->arenas.back());
 	for (auto &c : ctx->cscratch)
 		cudaFree(c.p);
 	cudaFree(ctx->d_ctl);
+	cudaFree(ctx->d_moved);
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
 }
@@ -291,6 +322,7 @@ int lz4e_b200_copy_h2d(lz4e_b200_ctx *ctx, void *stream, void *dst_dev,
 	cudaSetDevice(ctx->device);
 	CU(ctx, cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice,
 				pick(ctx, stream)));
+	ctx->h2d_bytes += bytes;
 	return LZ4E_B200_OK;
 }
 
@@ -300,6 +332,7 @@ int lz4e_b200_copy_d2h(lz4e_b200_ctx *ctx, void *stream, void *dst_host,
 	cudaSetDevice(ctx->device);
 	CU(ctx, cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost,
 				pick(ctx, stream)));
+	ctx->d2h_bytes += bytes;
 	return LZ4E_B200_OK;
 }
 
@@ -333,6 +366,29 @@ void *lz4e_b200_event_create(lz4e_b200_ctx *ctx)
 		return nullptr;
 	}
 	return (void *)e;
+}
+
+void *lz4e_b200_event_create_timed(lz4e_b200_ctx *ctx)
+{
+	cudaEvent_t e = nullptr;
+
+	cudaSetDevice(ctx->device);
+	if (cudaEventCreate(&e) != cudaSuccess) {
+		set_err(ctx, "cudaEventCreate failed");
+		return nullptr;
+	}
+	return (void *)e;
+}
+
+/* milliseconds from `from` to `to` (both recorded and completed), < 0 on error */
+float lz4e_b200_event_elapsed_ms(lz4e_b200_ctx *ctx, void *from, void *to)
+{
+	float ms = -1.0f;
+
+	cudaSetDevice(ctx->device);
+	if (cudaEventElapsedTime(&ms, (cudaEvent_t)from, (cudaEvent_t)to) != cudaSuccess)
+		return -1.0f;
+	return ms;
 }
 
 void lz4e_b200_event_destroy(lz4e_b200_ctx *ctx, void *event)
@@ -816,6 +872,85 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 	}
 	ctx->launches++;
 	return LZ4E_B200_OK;
+}
+
+int lz4e_b200_xfer_dev(lz4e_b200_ctx *ctx, void *stream,
+		       const struct lz4e_b200_dev_bvec *bvecs,
+		       const struct lz4e_b200_dev_iter *iters, const int32_t *lens,
+		       uint32_t nblocks, int to_host)
+{
+	lz4e_xfer_args a;
+
+	if (!ctx)
+		return LZ4E_B200_ENODEV;
+	if (nblocks == 0)
+		return LZ4E_B200_OK;
+	cudaSetDevice(ctx->device);
+	a.bvecs = bvecs;
+	a.iters = iters;
+	a.lens = lens;
+	a.moved = ctx->d_moved + (to_host ? 1 : 0);
+	a.nblocks = nblocks;
+	a.to_host = to_host ? 1 : 0;
+	a.narenas = 0;
+	{
+		std::lock_guard<std::mutex> lk(ctx->mu);
+
+		for (lz4e_b200_arena *ar : ctx->arenas) {
+			if (a.narenas == LZ4E_XFER_MAX_ARENAS)
+				break;
+			a.ar[a.narenas].lo = (uint64_t)(uintptr_t)ar->dev;
+			a.ar[a.narenas].hi = (uint64_t)(uintptr_t)ar->dev + ar->npages * PAGE_SIZE;
+			a.ar[a.narenas].delta =
+				(uint64_t)(uintptr_t)ar->host - (uint64_t)(uintptr_t)ar->dev;
+			a.narenas++;
+		}
+	}
+	for (int i = a.narenas; i < LZ4E_XFER_MAX_ARENAS; i++)
+		a.ar[i].lo = a.ar[i].hi = a.ar[i].delta = 0;
+	if (a.narenas == 0) {
+		a.narenas = 1; /* ar[0] is an empty range: nothing matches */
+	}
+	if (lz4e_launch_xfer(&a, ctx->sm_count, pick(ctx, stream))) {
+		set_err(ctx, "transfer kernel launch failed: %s",
+			cudaGetErrorString(cudaGetLastError()));
+		return LZ4E_B200_EIO;
+	}
+	ctx->launches++;
+	return LZ4E_B200_OK;
+}
+
+int lz4e_b200_traffic(lz4e_b200_ctx *ctx, uint64_t *h2d_bytes, uint64_t *d2h_bytes)
+{
+	unsigned long long m[2] = { 0, 0 };
+
+	if (!ctx)
+		return LZ4E_B200_ENODEV;
+	cudaSetDevice(ctx->device);
+	CU(ctx, cudaMemcpy(m, ctx->d_moved, sizeof(m), cudaMemcpyDeviceToHost));
+	if (h2d_bytes)
+		*h2d_bytes = ctx->h2d_bytes.load() + m[0];
+	if (d2h_bytes)
+		*d2h_bytes = ctx->d2h_bytes.load() + m[1];
+	return LZ4E_B200_OK;
+}
+
+void *lz4e_ctx_attach(lz4e_b200_ctx *ctx, int slot, size_t bytes,
+		      void (*dtor)(lz4e_b200_ctx *, void *))
+{
+	std::lock_guard<std::mutex> lk(ctx->mu);
+
+	for (auto &at : ctx->attached)
+		if (at.slot == slot)
+			return at.p;
+	if (!bytes)
+		return nullptr;
+	void *p = calloc(1, bytes);
+
+	if (!p)
+		return nullptr;
+	ctx->attached.push_back({ slot, p, dtor });
+	return p;
 }
 
 void lz4e_b200_shard_range(uint64_t nblocks, uint32_t rank, uint32_t world,

@@ -36,4 +36,22 @@ int lz4e_launch_order(const struct lz4e_b200_dev_iter *src_iters,
 		      const struct lz4e_b200_dev_iter *dst_iters, uint32_t n, uint32_t *ctl,
 		      uint32_t *order, cudaStream_t stream);
 
+
+/* exact-byte host <-> device transfers by the SMs (lz4e_xfer.cu) */
+#define LZ4E_XFER_MAX_ARENAS 16
+struct lz4e_xfer_args {
+	const struct lz4e_b200_dev_bvec *bvecs; /* DEVICE addresses */
+	const struct lz4e_b200_dev_iter *iters;
+	const int32_t *lens; /* bytes per block (<= 0: none); NULL: bi_size */
+	unsigned long long *moved; /* byte counter, may be NULL */
+	uint32_t nblocks;
+	int to_host;
+	int narenas;
+	struct {
+		uint64_t lo, hi; /* device range of the arena's mirror */
+		uint64_t delta;	 /* host address = device address + delta (mod 2^64) */
+	} ar[LZ4E_XFER_MAX_ARENAS];
+};
+int lz4e_launch_xfer(const lz4e_xfer_args *a, int sm_count, cudaStream_t stream);
+
 #endif

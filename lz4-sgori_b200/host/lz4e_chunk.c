@@ -12,6 +12,7 @@
 
 #include "../../include/lz4e.h"
 #include "../../include/lz4e_chunk.h"
+#include "lz4e_internal.h"
 
 /* ---- buffer pool: pinned pages with a device mirror ------------------------- */
 
@@ -33,6 +34,23 @@ static struct {
 	size_t live;
 	int ready;
 } pool;
+
+/* the pool's context is being destroyed: the pool goes with it (chunks still
+ * alive keep dangling buffers — a caller bug, reported) */
+static void pool_ctx_dtor(lz4e_b200_ctx *ctx, void *p)
+{
+	(void)p;
+	pthread_mutex_lock(&p_mu);
+	if (pool.ready && pool.ctx == ctx) {
+		if (pool.live)
+			fprintf(stderr, "lz4e_chunk: context destroyed with %zu pool buffers live\n",
+				pool.live);
+		lz4e_b200_arena_destroy(pool.arena);
+		free(pool.next);
+		memset(&pool, 0, sizeof(pool));
+	}
+	pthread_mutex_unlock(&p_mu);
+}
 
 static int pool_init_locked(lz4e_b200_ctx *ctx, size_t pool_pages)
 {
@@ -58,6 +76,7 @@ static int pool_init_locked(lz4e_b200_ctx *ctx, size_t pool_pages)
 		return -ENOMEM;
 	}
 	pool.ctx = ctx;
+	lz4e_ctx_attach(ctx, LZ4E_ATTACH_CHUNK_POOL, 8, pool_ctx_dtor);
 	pool.base = (uint8_t *)lz4e_b200_arena_pages(pool.arena);
 	pool.npages = pool_pages;
 	pool.bump = 0;
@@ -290,7 +309,8 @@ static void call_ws_free(struct call_ws *w)
 
 enum { OP_COMPRESS, OP_COMPRESS_EXT, OP_DECOMPRESS };
 
-static int chunk_batch(struct lz4e_chunk **chunks, size_t n, int *status, int op)
+static int chunk_batch(struct lz4e_chunk **chunks, size_t n, int *status, int op,
+		       unsigned int extra_flags)
 {
 	struct call_ws w;
 	lz4e_b200_ctx *ctx = chunk_ctx();
@@ -343,7 +363,7 @@ static int chunk_batch(struct lz4e_chunk **chunks, size_t n, int *status, int op
 		 * copy must not replace them with the device mirror's stale bytes:
 		 * ask for the range to be uploaded first.  A batch that owns every
 		 * live pool buffer (the request path below) skips that. */
-		unsigned int flags = 0;
+		unsigned int flags = extra_flags;
 		size_t mine = 0, live;
 
 		for (i = 0; i < n; i++)
@@ -392,24 +412,24 @@ static int chunk_batch(struct lz4e_chunk **chunks, size_t n, int *status, int op
 
 int lz4e_chunk_compress_batch(struct lz4e_chunk **chunks, size_t n, int *status)
 {
-	return chunk_batch(chunks, n, status, OP_COMPRESS);
+	return chunk_batch(chunks, n, status, OP_COMPRESS, 0);
 }
 
 int lz4e_chunk_compress_ext_batch(struct lz4e_chunk **chunks, size_t n, int *status)
 {
-	return chunk_batch(chunks, n, status, OP_COMPRESS_EXT);
+	return chunk_batch(chunks, n, status, OP_COMPRESS_EXT, 0);
 }
 
 int lz4e_chunk_decompress_batch(struct lz4e_chunk **chunks, size_t n, int *status)
 {
-	return chunk_batch(chunks, n, status, OP_DECOMPRESS);
+	return chunk_batch(chunks, n, status, OP_DECOMPRESS, 0);
 }
 
 int lz4e_chunk_compress(struct lz4e_chunk *chunk)
 {
 	int st = -EIO;
 
-	chunk_batch(&chunk, 1, &st, OP_COMPRESS);
+	chunk_batch(&chunk, 1, &st, OP_COMPRESS, 0);
 	return st;
 }
 
@@ -417,7 +437,7 @@ int lz4e_chunk_compress_ext(struct lz4e_chunk *chunk)
 {
 	int st = -EIO;
 
-	chunk_batch(&chunk, 1, &st, OP_COMPRESS_EXT);
+	chunk_batch(&chunk, 1, &st, OP_COMPRESS_EXT, 0);
 	return st;
 }
 
@@ -425,7 +445,7 @@ int lz4e_chunk_decompress(struct lz4e_chunk *chunk)
 {
 	int st = -EIO;
 
-	chunk_batch(&chunk, 1, &st, OP_DECOMPRESS);
+	chunk_batch(&chunk, 1, &st, OP_DECOMPRESS, 0);
 	return st;
 }
 
@@ -591,7 +611,8 @@ int lz4e_dev_submit_writes(struct lz4e_dev *dev, struct bio **bios, size_t n, in
 		live[i++] = live[k];
 	}
 	nlive = i;
-	lz4e_chunk_decompress_batch(live, nlive, st);
+	/* the compressed bytes are still current in the device mirror */
+	chunk_batch(live, nlive, st, OP_DECOMPRESS, LZ4E_B200_F_SRC_RESIDENT);
 	pthread_mutex_lock(&dev->mu);
 	for (k = 0; k < nlive; k++) {
 		struct bio *ob = bios[map[k]];

@@ -21,6 +21,7 @@
 
 #include "../../include/lz4e.h"
 #include "../../include/lz4e_b200.h"
+#include "lz4e_internal.h"
 
 #define MAX_ARENAS 16
 #define NLANES 3 /* chunks in flight: upload / kernel / download overlap */
@@ -53,10 +54,12 @@ struct side {
 	struct lz4e_b200_dev_iter *it;
 	size_t nbv;
 	struct range ar[MAX_ARENAS];
+	size_t sum[MAX_ARENAS]; /* bytes of this side's segments inside each arena */
 	struct bounce *bn;
 	size_t nbn, cap_bn;
 	size_t bounce_bytes;
 	uint32_t max_size;
+	int stage_all;	/* pack every segment (arena pages too) into the staging buffer */
 	int all_linear; /* every block is a single segment */
 	int any_u16;	/* some block would select byU16 (compress source) */
 };
@@ -71,8 +74,12 @@ struct side {
  */
 struct lane {
 	void *stream, *ev_kernel;
+	void *ev_t[4]; /* LZ4E_B200_TRACE=2: start, uploads done, kernel done, results down */
+	double t_submit;
+	size_t chunk_no, chunk_bytes;
 	uint8_t *pin, *dev, *bounce;
-	size_t pin_bytes, bounce_bytes;
+	uint8_t *stage; /* pinned image of the source part of `bounce` */
+	size_t pin_bytes, bounce_bytes, stage_bytes;
 	int busy;
 	struct lz4e_b200_req *reqs;
 	size_t n;
@@ -80,57 +87,226 @@ struct lane {
 	size_t o_ret, o_end;
 };
 
-/* one workspace per process, serialised: a lazily created resource pool
- * behind a lock (SURVEY.md section 8b "Threading") */
-static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
-static struct {
-	lz4e_b200_ctx *ctx;
-	struct lane lane[NLANES];
-} g_ws;
+/*
+ * One workspace per CONTEXT (attached to it, released by
+ * lz4e_b200_ctx_destroy): batches on different GPUs of one process run side by
+ * side, batches on the same context take turns (SURVEY.md section 8b
+ * "Threading": callers in many task contexts share a lazily created pool).
+ */
+#define MAX_WORKERS 16
 
-static void ws_drop(void)
+/* a few helper threads per context for the one host-side job that is pure
+ * memory traffic: packing scattered source bytes into a lane's pinned staging
+ * buffer (pack_run) */
+struct workers {
+	pthread_t th[MAX_WORKERS];
+	pthread_mutex_t mu;
+	pthread_cond_t go, done;
+	int n, started, quit;
+	unsigned long gen;
+	int pending;
+	/* the job: entries [0, count) of bn, split in n + 1 contiguous parts */
+	const struct bounce *bn;
+	size_t count;
+	uint8_t *base;
+};
+
+struct host_ws {
+	pthread_mutex_t mu;
+	int ready;
+	struct workers wk;
+	struct lane lane[NLANES];
+	void *ev_batch; /* LZ4E_B200_TRACE=2: start of the batch on the device */
+	int tracing;
+	double t_batch;
+	/* LZ4E_B200_TRACE=1: where a batch spends its host time (stderr) */
+	struct {
+		double build, enqueue, wait, pack;
+		size_t bulk_up, bulk_down, kern_up, kern_down, packed_up; /* chunks per mode */
+	} trace;
+};
+
+static pthread_mutex_t g_init_mu = PTHREAD_MUTEX_INITIALIZER;
+
+static void pack_part(const struct bounce *bn, size_t count, uint8_t *base, int part, int parts)
 {
+	size_t lo = count * (size_t)part / (size_t)parts;
+	const size_t hi = count * ((size_t)part + 1) / (size_t)parts;
+
+	for (; lo < hi; lo++)
+		memcpy(base + bn[lo].dev_off, bn[lo].host, bn[lo].len);
+}
+
+struct worker_arg {
+	struct workers *wk;
+	int idx;
+};
+
+static void *worker_main(void *p)
+{
+	struct worker_arg *wa = p;
+	struct workers *wk = wa->wk;
+	const int idx = wa->idx;
+	unsigned long seen = 0;
+
+	free(wa);
+	pthread_mutex_lock(&wk->mu);
+	for (;;) {
+		while (!wk->quit && wk->gen == seen)
+			pthread_cond_wait(&wk->go, &wk->mu);
+		if (wk->quit)
+			break;
+		seen = wk->gen;
+		pthread_mutex_unlock(&wk->mu);
+		pack_part(wk->bn, wk->count, wk->base, idx + 1, wk->n + 1);
+		pthread_mutex_lock(&wk->mu);
+		if (--wk->pending == 0)
+			pthread_cond_signal(&wk->done);
+	}
+	pthread_mutex_unlock(&wk->mu);
+	return NULL;
+}
+
+static void workers_start(struct workers *wk)
+{
+	const char *e = getenv("LZ4E_B200_HOST_THREADS");
+	int want = e ? atoi(e) : 4, i;
+
+	pthread_mutex_init(&wk->mu, NULL);
+	pthread_cond_init(&wk->go, NULL);
+	pthread_cond_init(&wk->done, NULL);
+	wk->started = 1;
+	if (want > MAX_WORKERS + 1)
+		want = MAX_WORKERS + 1;
+	for (i = 0; i + 1 < want; i++) { /* the calling thread is one of them */
+		struct worker_arg *wa = malloc(sizeof(*wa));
+
+		if (!wa)
+			break;
+		wa->wk = wk;
+		wa->idx = wk->n;
+		if (pthread_create(&wk->th[wk->n], NULL, worker_main, wa)) {
+			free(wa);
+			break;
+		}
+		wk->n++;
+	}
+}
+
+static void workers_stop(struct workers *wk)
+{
+	int i;
+
+	if (!wk->started)
+		return;
+	pthread_mutex_lock(&wk->mu);
+	wk->quit = 1;
+	pthread_cond_broadcast(&wk->go);
+	pthread_mutex_unlock(&wk->mu);
+	for (i = 0; i < wk->n; i++)
+		pthread_join(wk->th[i], NULL);
+	pthread_cond_destroy(&wk->go);
+	pthread_cond_destroy(&wk->done);
+	pthread_mutex_destroy(&wk->mu);
+	wk->started = 0;
+}
+
+/* copy every bn[i] (host bytes) to base + bn[i].dev_off, with the helpers when
+ * the job is large enough to pay for waking them */
+static void pack_run(struct workers *wk, const struct bounce *bn, size_t count, uint8_t *base,
+		     size_t bytes)
+{
+	if (!count)
+		return;
+	if (wk->n == 0 || bytes < ((size_t)1 << 20)) {
+		pack_part(bn, count, base, 0, 1);
+		return;
+	}
+	pthread_mutex_lock(&wk->mu);
+	wk->bn = bn;
+	wk->count = count;
+	wk->base = base;
+	wk->pending = wk->n;
+	wk->gen++;
+	pthread_cond_broadcast(&wk->go);
+	pthread_mutex_unlock(&wk->mu);
+	pack_part(bn, count, base, 0, wk->n + 1);
+	pthread_mutex_lock(&wk->mu);
+	while (wk->pending)
+		pthread_cond_wait(&wk->done, &wk->mu);
+	pthread_mutex_unlock(&wk->mu);
+}
+
+static void ws_dtor(lz4e_b200_ctx *ctx, void *p)
+{
+	struct host_ws *ws = p;
 	int l;
 
-	if (!g_ws.ctx)
+	if (!ws->ready)
 		return;
+	workers_stop(&ws->wk);
 	for (l = 0; l < NLANES; l++) {
-		struct lane *ln = &g_ws.lane[l];
+		struct lane *ln = &ws->lane[l];
 
-		lz4e_b200_host_free(g_ws.ctx, ln->pin);
-		lz4e_b200_dev_free(g_ws.ctx, ln->dev);
-		lz4e_b200_dev_free(g_ws.ctx, ln->bounce);
+		lz4e_b200_host_free(ctx, ln->stage);
+		lz4e_b200_host_free(ctx, ln->pin);
+		lz4e_b200_dev_free(ctx, ln->dev);
+		lz4e_b200_dev_free(ctx, ln->bounce);
 		if (ln->ev_kernel)
-			lz4e_b200_event_destroy(g_ws.ctx, ln->ev_kernel);
+			lz4e_b200_event_destroy(ctx, ln->ev_kernel);
+		for (int k = 0; k < 4; k++)
+			if (ln->ev_t[k])
+				lz4e_b200_event_destroy(ctx, ln->ev_t[k]);
 		if (ln->stream)
-			lz4e_b200_stream_destroy(g_ws.ctx, ln->stream);
+			lz4e_b200_stream_destroy(ctx, ln->stream);
 		free(ln->src.bn);
 		free(ln->dst.bn);
 	}
-	memset(&g_ws, 0, sizeof(g_ws));
+	if (ws->ev_batch)
+		lz4e_b200_event_destroy(ctx, ws->ev_batch);
+	pthread_mutex_destroy(&ws->mu);
+	ws->ready = 0;
 }
 
-static int ws_bind(lz4e_b200_ctx *ctx)
+/* the context's workspace, created on first use; NULL when that fails */
+static struct host_ws *ws_get(lz4e_b200_ctx *ctx)
 {
-	int l;
+	struct host_ws *ws = lz4e_ctx_attach(ctx, LZ4E_ATTACH_HOST_WS, sizeof(*ws), ws_dtor);
+	int l, ok = 1;
 
-	if (g_ws.ctx == ctx)
-		return LZ4E_B200_OK;
-	ws_drop();
-	g_ws.ctx = ctx;
-	for (l = 0; l < NLANES; l++) {
-		g_ws.lane[l].stream = lz4e_b200_stream_create(ctx);
-		g_ws.lane[l].ev_kernel = lz4e_b200_event_create(ctx);
-		if (!g_ws.lane[l].stream || !g_ws.lane[l].ev_kernel)
-			return LZ4E_B200_EIO;
+	if (!ws)
+		return NULL;
+	pthread_mutex_lock(&g_init_mu);
+	if (!ws->ready) {
+		for (l = 0; l < NLANES; l++) {
+			ws->lane[l].stream = lz4e_b200_stream_create(ctx);
+			ws->lane[l].ev_kernel = lz4e_b200_event_create(ctx);
+			if (!ws->lane[l].stream || !ws->lane[l].ev_kernel)
+				ok = 0;
+		}
+		if (ok) {
+			pthread_mutex_init(&ws->mu, NULL);
+			workers_start(&ws->wk);
+			ws->ready = 1;
+		}
 	}
-	return LZ4E_B200_OK;
+	pthread_mutex_unlock(&g_init_mu);
+	return ws->ready ? ws : NULL;
 }
 
 /* the lane is idle when this is called */
 static int lane_reserve(lz4e_b200_ctx *ctx, struct lane *ln, size_t pin_bytes,
-			size_t bounce_bytes)
+			size_t bounce_bytes, size_t stage_bytes)
 {
+	if (stage_bytes > ln->stage_bytes) {
+		const size_t want = stage_bytes + stage_bytes / 4 + 4096;
+
+		lz4e_b200_host_free(ctx, ln->stage);
+		ln->stage = lz4e_b200_host_alloc(ctx, want);
+		ln->stage_bytes = ln->stage ? want : 0;
+		if (!ln->stage)
+			return LZ4E_B200_ENOMEM;
+	}
 	if (pin_bytes > ln->pin_bytes) {
 		const size_t want = pin_bytes + pin_bytes / 4 + 4096;
 
@@ -209,6 +385,38 @@ static int ranges_overlap(const struct range *a, const struct range *b)
 	return 0;
 }
 
+/* hull and byte count of the host addresses a side's segments cover */
+struct span {
+	uintptr_t lo, hi;
+	uint64_t sum;
+};
+
+/* count_bvecs() that also grows the span */
+static size_t scan_bvecs(const struct bio_vec *bv, const struct bvec_iter *it, struct span *sp)
+{
+	size_t n = 0;
+	unsigned int left = it->bi_size, idx = it->bi_idx, done = it->bi_bvec_done;
+
+	while (left) {
+		const struct bio_vec *v = &bv[idx];
+		unsigned int take = v->bv_len - done;
+		const uintptr_t a = (uintptr_t)page_address(v->bv_page) + v->bv_offset + done;
+
+		if (take > left)
+			take = left;
+		if (a < sp->lo)
+			sp->lo = a;
+		if (a + take > sp->hi)
+			sp->hi = a + take;
+		sp->sum += take;
+		left -= take;
+		done = 0;
+		idx++;
+		n++;
+	}
+	return n ? n : 1;
+}
+
 /* number of bio_vecs under an iterator (LZ4E_for_each_bvec) */
 static size_t count_bvecs(const struct bio_vec *bv, const struct bvec_iter *it)
 {
@@ -226,30 +434,6 @@ static size_t count_bvecs(const struct bio_vec *bv, const struct bvec_iter *it)
 		n++;
 	}
 	return n ? n : 1; /* an empty block still gets one (dummy) entry */
-}
-
-/* arena byte ranges a block's segments touch (no tables built) */
-static void side_ranges(struct arena_set *as, struct range *r,
-			const struct bio_vec *bv, const struct bvec_iter *it)
-{
-	unsigned int left = it->bi_size, idx = it->bi_idx, done = it->bi_bvec_done;
-
-	while (left) {
-		const struct bio_vec *v = &bv[idx];
-		unsigned int take = v->bv_len - done;
-		uint8_t *h = (uint8_t *)page_address(v->bv_page) + v->bv_offset + done;
-		int k;
-
-		if (take > left)
-			take = left;
-		k = arena_find(as, h, take);
-		if (k >= 0)
-			range_add(&r[k], (size_t)(h - as->v[k].host),
-				  (size_t)(h - as->v[k].host) + take);
-		left -= take;
-		done = 0;
-		idx++;
-	}
 }
 
 /* Append the bio_vecs block `blk` covers to side s.  The device iterator is
@@ -287,7 +471,7 @@ static int side_add(struct arena_set *as, struct side *s, uint32_t blk,
 			take = left;
 		if (nseg >= 16 || v->bv_len > 4096)
 			u16 = 0;
-		k = arena_find(as, h + done, take);
+		k = s->stage_all ? -1 : arena_find(as, h + done, take);
 		if (k >= 0) {
 			const size_t off = (size_t)((h + done) - as->v[k].host);
 
@@ -295,6 +479,7 @@ static int side_add(struct arena_set *as, struct side *s, uint32_t blk,
 			o->addr = (uint64_t)(uintptr_t)(as->v[k].dev + off) - done;
 			o->rsvd = 0;
 			range_add(&s->ar[k], off, off + take);
+			s->sum[k] += take;
 		} else {
 			/* bounce: keep the host address's alignment mod 16 */
 			size_t off = (s->bounce_bytes + 15) & ~(size_t)15;
@@ -365,11 +550,6 @@ static double now_ms(void)
 	return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
 }
 
-/* LZ4E_B200_TRACE=1: where a batch spends its host time (stderr) */
-static struct {
-	double build, enqueue, wait;
-} g_trace;
-
 static size_t al256(size_t x)
 {
 	return (x + 255) & ~(size_t)255;
@@ -393,9 +573,82 @@ static int copy_ranges(lz4e_b200_ctx *ctx, struct arena_set *as, void *stream,
 	return rc;
 }
 
+/*
+ * A side is DENSE when, in every arena it touches, its segments tile the byte
+ * range they span: a copy-engine copy of that range then moves no byte that
+ * belongs to somebody else.  Everything else goes through the exact-byte
+ * transfer kernel (lz4e_b200_xfer_dev).
+ */
+static int side_dense(const struct side *s)
+{
+	int k;
+
+	for (k = 0; k < MAX_ARENAS; k++)
+		if (s->ar[k].hi - s->ar[k].lo != s->sum[k])
+			return 0;
+	return 1;
+}
+
+static int side_in_arenas(const struct side *s)
+{
+	int k;
+
+	for (k = 0; k < MAX_ARENAS; k++)
+		if (s->sum[k])
+			return 1;
+	return 0;
+}
+
+/* LZ4E_B200_XFER: 0 = copy engines only (ranges, the round-1 behaviour),
+ * 1 = default (kernel for compressed bytes and sparse sides, copy engines for
+ * dense uncompressed sides), 2 = transfer kernel for everything */
+static int xfer_mode(void)
+{
+	const char *e = getenv("LZ4E_B200_XFER");
+	const int mode = e ? atoi(e) : 1;
+
+	return mode < 0 || mode > 2 ? 1 : mode;
+}
+
+/* LZ4E_B200_SPARSE_SRC: how sources that do not tile their address range go
+ * up: "kernel" (transfer kernel, exact bytes), "pack" (host threads pack them
+ * into pinned staging, one copy-engine transfer), "hull" (copy engine over the
+ * whole range they span: also moves the bytes in between) */
+enum { SPARSE_KERNEL, SPARSE_PACK, SPARSE_HULL };
+
+static int sparse_src_mode(const struct side *s)
+{
+	const char *e = getenv("LZ4E_B200_SPARSE_SRC");
+	size_t sum = 0, span = 0;
+	int k;
+
+	if (e && !strcmp(e, "pack"))
+		return SPARSE_PACK;
+	if (e && !strcmp(e, "hull"))
+		return SPARSE_HULL;
+	if (e && !strcmp(e, "kernel"))
+		return SPARSE_KERNEL;
+	if (!s)
+		return SPARSE_KERNEL;
+	/*
+	 * Measured on B200 / PCIe 5 (profiles/r2k_e2e_timeline.md): SM reads of
+	 * host memory stop at about 30 GB/s and queue behind concurrent
+	 * device -> host writes (PCIe ordering), the copy engines read at 47-55
+	 * GB/s whatever else is going on; host threads pack at 16-20 GB/s.  So a
+	 * side that fills a quarter or more of the range it spans (compressed
+	 * 4 KiB blocks in their LZ4E_COMPRESSBOUND slots: 40 %) goes up as that
+	 * range, sparser ones through the kernel.
+	 */
+	for (k = 0; k < MAX_ARENAS; k++) {
+		sum += s->sum[k];
+		span += s->ar[k].hi - s->ar[k].lo;
+	}
+	return span && sum * 4 >= span ? SPARSE_HULL : SPARSE_KERNEL;
+}
+
 /* wait for a chunk and hand its results back to the caller's requests */
-static int lane_finish(lz4e_b200_ctx *ctx, struct lane *ln, int decompress,
-		       unsigned flags)
+static int lane_finish(lz4e_b200_ctx *ctx, struct host_ws *ws, struct lane *ln,
+		       int decompress, unsigned flags)
 {
 	const int32_t *rets = (const int32_t *)(ln->pin + ln->o_ret);
 	const struct lz4e_b200_dev_end *ends =
@@ -410,7 +663,18 @@ static int lane_finish(lz4e_b200_ctx *ctx, struct lane *ln, int decompress,
 	ln->busy = 0;
 	t0 = now_ms();
 	rc = lz4e_b200_sync(ctx, ln->stream);
-	g_trace.wait += now_ms() - t0;
+	ws->trace.wait += now_ms() - t0;
+	if (ws->tracing >= 2 && !rc && ln->ev_t[0])
+		fprintf(stderr,
+			"lz4e_b200:   chunk %3zu (%6.1f MiB) host: submitted at %6.2f ms, finished at "
+			"%6.2f; device: starts %6.2f, uploads %5.2f, kernel (incl. wait for the one "
+			"before) %5.2f, results down %5.2f ms\n",
+			ln->chunk_no, ln->chunk_bytes / 1048576.0, ln->t_submit - ws->t_batch,
+			now_ms() - ws->t_batch,
+			lz4e_b200_event_elapsed_ms(ctx, ws->ev_batch, ln->ev_t[0]),
+			lz4e_b200_event_elapsed_ms(ctx, ln->ev_t[0], ln->ev_t[1]),
+			lz4e_b200_event_elapsed_ms(ctx, ln->ev_t[1], ln->ev_t[2]),
+			lz4e_b200_event_elapsed_ms(ctx, ln->ev_t[2], ln->ev_t[3]));
 	/* bounced destination segments: bring back exactly the bytes produced */
 	for (i = 0; i < ln->dst.nbn && !rc; i++) {
 		const struct bounce *b = &ln->dst.bn[i];
@@ -444,13 +708,17 @@ static int lane_finish(lz4e_b200_ctx *ctx, struct lane *ln, int decompress,
 
 /* build the tables of one chunk in the lane's workspace and enqueue its
  * uploads, kernel and downloads on the lane's stream */
-static int lane_submit(lz4e_b200_ctx *ctx, struct arena_set *as, struct lane *ln,
-		       struct lz4e_b200_req *reqs, size_t n, size_t ns, size_t nd,
-		       unsigned flags, int decompress, void *prev_kernel)
+static int lane_submit(lz4e_b200_ctx *ctx, struct host_ws *ws, struct arena_set *as,
+		       struct lane *ln, struct lz4e_b200_req *reqs, size_t n, size_t ns,
+		       size_t nd, unsigned flags, int decompress, void *prev_kernel,
+		       int stage_src)
 {
 	size_t i, off, pin_bytes, o_sbv, o_dbv, o_sit, o_dit, sb;
-	int rc = LZ4E_B200_OK, l;
+	int rc = LZ4E_B200_OK, l, src_kernel, dst_kernel;
+	const int mode = xfer_mode();
 	double t0 = now_ms(), t1;
+	struct lz4e_b200_dev_bvec *d_sbv, *d_dbv;
+	struct lz4e_b200_dev_iter *d_sit, *d_dit;
 
 	off = 0;
 	o_sbv = off; off = al256(off + ns * sizeof(struct lz4e_b200_dev_bvec));
@@ -460,13 +728,14 @@ static int lane_submit(lz4e_b200_ctx *ctx, struct arena_set *as, struct lane *ln
 	ln->o_ret = off; off = al256(off + n * sizeof(int32_t));
 	ln->o_end = off; off = al256(off + n * sizeof(struct lz4e_b200_dev_end));
 	pin_bytes = off;
-	rc = lane_reserve(ctx, ln, pin_bytes, 0);
+	rc = lane_reserve(ctx, ln, pin_bytes, 0, 0);
 	if (rc)
 		return rc;
 	ln->reqs = reqs;
 	ln->n = n;
 	side_reset(&ln->src);
 	side_reset(&ln->dst);
+	ln->src.stage_all = stage_src;
 	ln->src.bv = (struct lz4e_b200_dev_bvec *)(ln->pin + o_sbv);
 	ln->dst.bv = (struct lz4e_b200_dev_bvec *)(ln->pin + o_dbv);
 	ln->src.it = (struct lz4e_b200_dev_iter *)(ln->pin + o_sit);
@@ -478,65 +747,109 @@ static int lane_submit(lz4e_b200_ctx *ctx, struct arena_set *as, struct lane *ln
 	}
 	if (rc)
 		return rc;
-	t1 = now_ms();
-	g_trace.build += t1 - t0;
+	d_sbv = (struct lz4e_b200_dev_bvec *)(ln->dev + o_sbv);
+	d_dbv = (struct lz4e_b200_dev_bvec *)(ln->dev + o_dbv);
+	d_sit = (struct lz4e_b200_dev_iter *)(ln->dev + o_sit);
+	d_dit = (struct lz4e_b200_dev_iter *)(ln->dev + o_dit);
 	/*
-	 * Chunks still in flight: a bulk copy of this chunk must not cross bytes a
-	 * running chunk produces (or the other way round).  Callers that interleave
-	 * the pages of different chunks inside one arena lose the overlap, not the
-	 * result.
+	 * How the pages travel.  Source: copy engines when the side is dense
+	 * (uncompressed blocks laid end to end), the transfer kernel otherwise —
+	 * compressed blocks sitting in LZ4E_COMPRESSBOUND-sized slots, scattered
+	 * segments with foreign pages in between.  Destination: a compressor's
+	 * output always through the kernel (rets[b] bytes per block, known only on
+	 * the device); a decompressor's through the copy engines when dense.
+	 * LZ4E_B200_F_DST_PRESERVE asks that no other host byte changes: kernel.
+	 */
+	src_kernel = mode == 2 || (mode == 1 && !side_dense(&ln->src) &&
+				   sparse_src_mode(&ln->src) != SPARSE_HULL);
+	dst_kernel = mode == 2 ||
+		     (mode == 1 && (!decompress || !side_dense(&ln->dst) ||
+				    (flags & LZ4E_B200_F_DST_PRESERVE)));
+	if (!side_in_arenas(&ln->src))
+		src_kernel = 0;
+	if (!side_in_arenas(&ln->dst))
+		dst_kernel = 0;
+	t1 = now_ms();
+	ws->trace.build += t1 - t0;
+	/*
+	 * Chunks still in flight: a copy of this chunk must not cross bytes a
+	 * running chunk produces (or the other way round).  The ranges are hulls,
+	 * so callers that interleave the pages of different chunks inside one
+	 * arena lose the overlap, not the result.
 	 */
 	for (l = 0; l < NLANES && !rc; l++) {
-		struct lane *o = &g_ws.lane[l];
+		struct lane *o = &ws->lane[l];
 
 		if (o == ln || !o->busy)
 			continue;
 		if (ranges_overlap(ln->src.ar, o->dst.ar) || ranges_overlap(ln->dst.ar, o->dst.ar) ||
 		    ranges_overlap(ln->dst.ar, o->src.ar))
-			rc = lane_finish(ctx, o, decompress, flags);
+			rc = lane_finish(ctx, ws, o, decompress, flags);
 	}
 	if (rc)
 		return rc;
 	/* bounce space: source segments first, destination segments after */
 	sb = (ln->src.bounce_bytes + 255) & ~(size_t)255;
 	if (ln->src.nbn || ln->dst.nbn) {
-		rc = lane_reserve(ctx, ln, pin_bytes, sb + ln->dst.bounce_bytes + 256);
+		rc = lane_reserve(ctx, ln, pin_bytes, sb + ln->dst.bounce_bytes + 256,
+				  ln->src.bounce_bytes);
 		if (rc)
 			return rc;
 		side_rebase_bounce(&ln->src, ln->bounce);
 		side_rebase_bounce(&ln->dst, ln->bounce + sb);
-		for (i = 0; i < ln->src.nbn && !rc; i++)
-			rc = lz4e_b200_copy_h2d(ctx, ln->stream, ln->bounce + ln->src.bn[i].dev_off,
-						ln->src.bn[i].host, ln->src.bn[i].len);
+		if (ln->src.nbn) {
+			/* scattered source bytes: packed into pinned memory by the
+			 * host threads, then ONE copy-engine transfer */
+			const double tp = now_ms();
+
+			pack_run(&ws->wk, ln->src.bn, ln->src.nbn, ln->stage, ln->src.bounce_bytes);
+			ws->trace.pack += now_ms() - tp;
+			rc = lz4e_b200_copy_h2d(ctx, ln->stream, ln->bounce, ln->stage,
+						ln->src.bounce_bytes);
+			ws->trace.packed_up++;
+		}
 		for (i = 0; i < ln->dst.nbn; i++)
 			ln->dst.bn[i].dev_off += sb;
 	}
-	/* pages of arenas: one bulk copy per arena and direction */
-	if (!rc && !(flags & LZ4E_B200_F_SRC_RESIDENT))
-		rc = copy_ranges(ctx, as, ln->stream, ln->src.ar, 1);
-	if (!rc && (flags & LZ4E_B200_F_DST_PRESERVE))
-		rc = copy_ranges(ctx, as, ln->stream, ln->dst.ar, 1);
+	ln->t_submit = now_ms();
+	if (ws->tracing >= 2) {
+		int k;
+
+		for (k = 0; k < 4; k++)
+			if (!ln->ev_t[k])
+				ln->ev_t[k] = lz4e_b200_event_create_timed(ctx);
+		if (ln->ev_t[0])
+			lz4e_b200_event_record(ctx, ln->ev_t[0], ln->stream);
+	}
+	/* tables first: the transfer kernel reads them */
 	if (!rc)
 		rc = lz4e_b200_copy_h2d(ctx, ln->stream, ln->dev, ln->pin, ln->o_ret);
+	if (!rc && !(flags & LZ4E_B200_F_SRC_RESIDENT) && side_in_arenas(&ln->src)) {
+		if (src_kernel) {
+			rc = lz4e_b200_xfer_dev(ctx, ln->stream, d_sbv, d_sit, NULL, (uint32_t)n, 0);
+			ws->trace.kern_up++;
+		} else {
+			rc = copy_ranges(ctx, as, ln->stream, ln->src.ar, 1);
+			ws->trace.bulk_up++;
+		}
+	}
+	if (!rc && !dst_kernel && (flags & LZ4E_B200_F_DST_PRESERVE))
+		rc = copy_ranges(ctx, as, ln->stream, ln->dst.ar, 1);
+	if (ws->tracing >= 2 && ln->ev_t[1])
+		lz4e_b200_event_record(ctx, ln->ev_t[1], ln->stream);
 	if (!rc && prev_kernel)
 		rc = lz4e_b200_stream_wait_event(ctx, ln->stream, prev_kernel);
 	if (rc)
 		return rc;
 	if (decompress) {
 		rc = lz4e_b200_decompress_dev(
-			ctx, ln->stream, (struct lz4e_b200_dev_bvec *)(ln->dev + o_sbv),
-			(struct lz4e_b200_dev_iter *)(ln->dev + o_sit),
-			(struct lz4e_b200_dev_bvec *)(ln->dev + o_dbv),
-			(struct lz4e_b200_dev_iter *)(ln->dev + o_dit), (uint32_t)n,
+			ctx, ln->stream, d_sbv, d_sit, d_dbv, d_dit, (uint32_t)n,
 			ln->src.max_size, ln->dst.max_size,
 			ln->dst.all_linear ? LZ4E_B200_DEV_DST_LINEAR : 0,
 			(int32_t *)(ln->dev + ln->o_ret));
 	} else {
 		rc = lz4e_b200_compress_dev(
-			ctx, ln->stream, (struct lz4e_b200_dev_bvec *)(ln->dev + o_sbv),
-			(struct lz4e_b200_dev_iter *)(ln->dev + o_sit),
-			(struct lz4e_b200_dev_bvec *)(ln->dev + o_dbv),
-			(struct lz4e_b200_dev_iter *)(ln->dev + o_dit), (uint32_t)n,
+			ctx, ln->stream, d_sbv, d_sit, d_dbv, d_dit, (uint32_t)n,
 			ln->src.max_size,
 			(ln->src.any_u16 ? 0 : LZ4E_B200_DEV_NO_BYU16) |
 				(ln->dst.all_linear ? LZ4E_B200_DEV_DST_LINEAR : 0),
@@ -545,20 +858,31 @@ static int lane_submit(lz4e_b200_ctx *ctx, struct arena_set *as, struct lane *ln
 	}
 	if (!rc)
 		rc = lz4e_b200_event_record(ctx, ln->ev_kernel, ln->stream);
+	if (ws->tracing >= 2 && ln->ev_t[2])
+		lz4e_b200_event_record(ctx, ln->ev_t[2], ln->stream);
+	if (!rc && !(flags & LZ4E_B200_F_DST_ON_DEVICE)) {
+		if (dst_kernel) {
+			rc = lz4e_b200_xfer_dev(ctx, ln->stream, d_dbv, d_dit,
+						(const int32_t *)(ln->dev + ln->o_ret), (uint32_t)n, 1);
+			ws->trace.kern_down++;
+		} else {
+			rc = copy_ranges(ctx, as, ln->stream, ln->dst.ar, 0);
+			ws->trace.bulk_down++;
+		}
+	}
 	if (!rc)
 		rc = lz4e_b200_copy_d2h(ctx, ln->stream, ln->pin + ln->o_ret, ln->dev + ln->o_ret,
 					pin_bytes - ln->o_ret);
-	if (!rc && !(flags & LZ4E_B200_F_DST_ON_DEVICE))
-		rc = copy_ranges(ctx, as, ln->stream, ln->dst.ar, 0);
+	if (ws->tracing >= 2 && ln->ev_t[3])
+		lz4e_b200_event_record(ctx, ln->ev_t[3], ln->stream);
 	ln->busy = 1; /* something may be enqueued even when rc != 0 */
-	g_trace.enqueue += now_ms() - t1;
+	ws->trace.enqueue += now_ms() - t1;
 	return rc;
 }
 
 /* bytes (source + destination capacity) per chunk: LZ4E_B200_CHUNK_MB, else a
  * sixteenth of the batch within [16, 256] MiB — small chunks pay per-chunk
- * launch/sync latency, large ones a longer pipeline fill (B200, PCIe 5: 1 GiB of
- * 4 KiB blocks takes 38 ms at 32 MiB, 33 ms at 128 MiB) */
+ * launch/sync latency, large ones a longer pipeline fill */
 static size_t chunk_target_bytes(uint64_t total)
 {
 	const char *e = getenv("LZ4E_B200_CHUNK_MB");
@@ -577,11 +901,12 @@ static int run_batch(lz4e_b200_ctx *ctx, struct lz4e_b200_req *reqs, size_t n,
 		     unsigned flags, int decompress)
 {
 	struct arena_set as;
+	struct host_ws *ws;
 	size_t i, first, nchunk = 0, target;
-	uint64_t total = 0;
+	uint64_t total = 0, done_bytes = 0;
 	void *prev_kernel = NULL;
 	int rc = LZ4E_B200_OK, l;
-	double t_start = 0, t_guard = 0;
+	double t_start = 0;
 
 	if (!ctx) {
 		fprintf(stderr, "lz4e_b200: no CUDA context: the LZ4E library has no CPU path\n");
@@ -593,84 +918,133 @@ static int run_batch(lz4e_b200_ctx *ctx, struct lz4e_b200_req *reqs, size_t n,
 		return LZ4E_B200_OK;
 	if (n > 0x7fffffffu)
 		return LZ4E_B200_EINVAL;
+	ws = ws_get(ctx);
+	if (!ws) {
+		for (i = 0; i < n; i++)
+			reqs[i].ret = decompress ? -1 : 0;
+		return LZ4E_B200_EIO;
+	}
 
-	pthread_mutex_lock(&g_mu);
+	pthread_mutex_lock(&ws->mu);
 	t_start = now_ms();
-	memset(&g_trace, 0, sizeof(g_trace));
-	rc = ws_bind(ctx);
-	if (rc)
-		goto out;
+	memset(&ws->trace, 0, sizeof(ws->trace));
+	{
+		const char *e = getenv("LZ4E_B200_TRACE");
+
+		ws->tracing = e ? atoi(e) : 0;
+		ws->t_batch = t_start;
+		if (ws->tracing >= 2) {
+			if (!ws->ev_batch)
+				ws->ev_batch = lz4e_b200_event_create_timed(ctx);
+			if (ws->ev_batch)
+				lz4e_b200_event_record(ctx, ws->ev_batch, ws->lane[0].stream);
+			else
+				ws->tracing = 1;
+		}
+	}
 	arena_set_init(ctx, &as);
-	for (i = 0; i < n; i++)
-		total += (uint64_t)reqs[i].src_iter->bi_size + reqs[i].dst_iter->bi_size;
+	{
+		/* size of the batch, estimated from a sample: walking a quarter of
+		 * a million requests before the first chunk is submitted costs a
+		 * millisecond of idle PCIe */
+		const size_t stride = n > 4096 ? n / 1024 : 1;
+		size_t cnt = 0;
+
+		for (i = 0; i < n; i += stride, cnt++)
+			total += (uint64_t)reqs[i].src_iter->bi_size + reqs[i].dst_iter->bi_size;
+		total = total / cnt * n;
+	}
 	target = chunk_target_bytes(total);
 	/* few blocks: one kernel (each block is one warp's serial work, so two
 	 * half-empty kernels one after the other only double the latency) */
 	if (n < 4096 && !getenv("LZ4E_B200_CHUNK_MB"))
 		target = (size_t)-1;
-	if (total > target) {
-		/*
-		 * More than one chunk: uploads of later chunks and downloads of
-		 * earlier ones will overlap in time.  That is only safe when no bulk
-		 * source range crosses a bulk destination range of the same arena;
-		 * otherwise the batch runs as a single chunk (all uploads, kernel,
-		 * all downloads).
-		 */
-		struct range sr[MAX_ARENAS], dr[MAX_ARENAS];
-
-		memset(sr, 0, sizeof(sr));
-		memset(dr, 0, sizeof(dr));
-		for (i = 0; i < n; i++) {
-			side_ranges(&as, sr, reqs[i].src, reqs[i].src_iter);
-			side_ranges(&as, dr, reqs[i].dst, reqs[i].dst_iter);
-		}
-		if (ranges_overlap(sr, dr))
-			target = (size_t)-1;
+	if (xfer_mode() == 0 && total > target) {
+		/* copy engines only: ranges of different chunks may cross; the
+		 * round-1 rule — one chunk unless sources and destinations are
+		 * apart — is kept for this diagnostic mode by running one chunk */
+		target = (size_t)-1;
 	}
-	t_guard = now_ms() - t_start;
 	for (first = 0; first < n && !rc;) {
-		struct lane *ln = &g_ws.lane[nchunk % NLANES];
+		struct lane *ln = &ws->lane[nchunk % NLANES];
 		size_t cnt = 0, ns = 0, nd = 0;
 		uint64_t bytes = 0;
+		/* the first chunks are smaller so that the first kernel starts
+		 * (and the last download ends) sooner */
+		size_t want = nchunk == 0 && target != (size_t)-1 ? target / 4
+			      : nchunk == 1 && target != (size_t)-1 ? target / 2
+								    : target;
 
-		while (first + cnt < n && (cnt == 0 || (bytes < target && cnt < (1u << 20)))) {
+		/* ... and the last ones shrink again: what is behind the last
+		 * upload (kernel, results down) is not overlapped by anything */
+		if (target != (size_t)-1 && nchunk >= 2) {
+			const uint64_t left = total > done_bytes ? total - done_bytes : 0;
+
+			if (left < 2 * (uint64_t)target)
+				want = left / 2 > target / 4 ? (size_t)(left / 2) : target / 4;
+		}
+
+		struct span sp = { (uintptr_t)-1, 0, 0 };
+		int stage_src;
+
+		while (first + cnt < n && (cnt == 0 || (bytes < want && cnt < (1u << 20)))) {
 			const struct lz4e_b200_req *q = &reqs[first + cnt];
 
-			ns += count_bvecs(q->src, q->src_iter);
+			ns += scan_bvecs(q->src, q->src_iter, &sp);
 			nd += count_bvecs(q->dst, q->dst_iter);
 			bytes += (uint64_t)q->src_iter->bi_size + q->dst_iter->bi_size;
 			cnt++;
 		}
-		rc = lane_finish(ctx, ln, decompress, flags);
+		/*
+		 * Sources that do not (nearly) tile the address range they span —
+		 * compressed blocks in LZ4E_COMPRESSBOUND-sized slots, segments
+		 * with foreign pages in between — are packed into pinned staging by
+		 * the host threads and go up in one copy: exactly their bytes, at
+		 * copy-engine speed.  (SM reads over PCIe, the transfer kernel in
+		 * the host -> device direction, stop at about 30 GB/s and stall
+		 * behind concurrent device -> host writes; it stays as the path for
+		 * sides that turn out sparse after a dense guess.)
+		 */
+		stage_src = xfer_mode() == 1 && sparse_src_mode(NULL) == SPARSE_PACK &&
+			    !(flags & LZ4E_B200_F_SRC_RESIDENT) && sp.sum &&
+			    (double)sp.sum < 0.97 * (double)(sp.hi - sp.lo);
+		rc = lane_finish(ctx, ws, ln, decompress, flags);
+		ln->chunk_no = nchunk;
+		ln->chunk_bytes = (size_t)bytes;
 		if (!rc)
-			rc = lane_submit(ctx, &as, ln, reqs + first, cnt, ns, nd, flags,
-					 decompress, prev_kernel);
+			rc = lane_submit(ctx, ws, &as, ln, reqs + first, cnt, ns, nd, flags,
+					 decompress, prev_kernel, stage_src);
 		prev_kernel = ln->ev_kernel;
+		done_bytes += bytes;
 		first += cnt;
 		nchunk++;
 	}
 	/* drain in submission order */
 	for (l = 0; l < NLANES; l++) {
-		struct lane *ln = &g_ws.lane[(nchunk + l) % NLANES];
-		const int r2 = lane_finish(ctx, ln, decompress, flags);
+		struct lane *ln = &ws->lane[(nchunk + l) % NLANES];
+		const int r2 = lane_finish(ctx, ws, ln, decompress, flags);
 
 		if (!rc)
 			rc = r2;
 	}
-	if (getenv("LZ4E_B200_TRACE"))
+	if (ws->tracing)
 		fprintf(stderr,
-			"lz4e_b200: %s batch of %zu in %zu chunks: %.2f ms (range check %.2f, "
-			"table build %.2f, enqueue %.2f, waiting %.2f)\n",
-			decompress ? "decompress" : "compress", n, nchunk, now_ms() - t_start,
-			t_guard, g_trace.build, g_trace.enqueue, g_trace.wait);
-out:
+			"lz4e_b200: dev %d %s batch of %zu in %zu chunks: %.2f ms (table build %.2f, "
+			"packing %.2f, enqueue %.2f, waiting %.2f); source up: %zu chunks "
+			"by copy engine, %zu packed + copy engine, %zu by kernel; results down: %zu "
+			"by copy engine, %zu by kernel\n",
+			lz4e_b200_ctx_device(ctx), decompress ? "decompress" : "compress", n, nchunk,
+			now_ms() - t_start, ws->trace.build, ws->trace.pack,
+			ws->trace.enqueue - ws->trace.pack,
+			ws->trace.wait, ws->trace.bulk_up, ws->trace.packed_up, ws->trace.kern_up,
+			ws->trace.bulk_down, ws->trace.kern_down);
 	if (rc) {
 		fprintf(stderr, "lz4e_b200: batch failed (%d): %s\n", rc,
 			lz4e_b200_strerror(ctx));
 		for (i = 0; i < n; i++)
 			reqs[i].ret = decompress ? -1 : 0;
 	}
-	pthread_mutex_unlock(&g_mu);
+	pthread_mutex_unlock(&ws->mu);
 	return rc;
 }
 

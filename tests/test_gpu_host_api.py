@@ -192,3 +192,124 @@ def test_compacted_output(ctx, ref_lib):
     for b in range(n):
         o = int(offs[b])
         assert np.array_equal(packed[o:o + int(rets[b])], ref_dst.read_block(b, ref_rets[b])), b
+
+
+@pytest.mark.parametrize("mode", ["1", "2"])
+def test_batch_moves_exact_bytes(ctx, ref_lib, mode, monkeypatch):
+    """The transfer kernel brings back rets[b] bytes per block and nothing else: without
+    LZ4E_B200_F_DST_PRESERVE every host byte the codec did not produce keeps its value, and the
+    PCIe byte counters show produced bytes, not destination slots."""
+    monkeypatch.setenv("LZ4E_B200_XFER", mode)
+    monkeypatch.setenv("LZ4E_B200_SPARSE_SRC", "kernel")  # default: the spanned range when >= 25 % full
+    monkeypatch.setenv("LZ4E_B200_CHUNK_MB", "2")
+    n = 2000
+    datas = [common.synth(4096, b & 3, 11 + b) for b in range(n)]
+    specs = [dict(sg.segs_single(4096), gap=0)] * n
+    dspecs = [dict(sg.segs_single(sg.compress_bound(4096)), gap=0)] * n
+    src = common.build_layout(_arena(ctx), specs, datas)
+    dst = common.build_layout(_arena(ctx), dspecs)
+    dst.arena.mem[:] = 0xEE
+    creqs, keep = pkg.make_reqs(src, dst)
+    ctx.sync()
+    h0, d0 = ctx.traffic()
+    assert ctx.compress_batch(creqs, flags=pkg.F_KEEP_ITERS) == 0, ctx.err()
+    ctx.sync()
+    h1, d1 = ctx.traffic()
+    rets = creqs["ret"].copy()
+    ref_dst, (ref_rets, _) = common.oracle_compress(ref_lib, src, dspecs)
+    assert np.array_equal(rets, ref_rets)
+    assert np.array_equal(dst.arena.mem, ref_dst.arena.mem[:len(dst.arena.mem)])  # 0xEE elsewhere
+    tables = n * 64 + 8 * 256 * 16
+    assert n * 4096 <= h1 - h0 <= n * 4096 + tables + 4096 * 16
+    assert int(rets.sum()) <= d1 - d0 <= int(rets.sum()) + n * 12 + 8 * 256 * 16
+    # decompress: only the compressed bytes go up
+    out = common.build_layout(_arena(ctx), specs)
+    csrc = sg.Layout(dst.arena, dst.bvecs, dst.first, dst.iters.copy(), dst.npages_used)
+    csrc.iters["bi_size"] = rets.astype(np.uint32)
+    dreqs, keep2 = pkg.make_reqs(csrc, out)
+    assert ctx.decompress_batch(dreqs) == 0, ctx.err()
+    ctx.sync()
+    h2, d2 = ctx.traffic()
+    assert int(rets.sum()) <= h2 - h1 <= int(rets.sum()) + tables
+    assert (dreqs["ret"] == 4096).all()
+    assert np.array_equal(out.arena.mem[:n * 4096], src.arena.mem[:n * 4096])
+
+
+@pytest.mark.parametrize("sparse", ["kernel", "hull", "pack"])
+def test_batch_sparse_source_modes(ctx, ref_lib, sparse, monkeypatch):
+    """The three ways a sparse source side can go up give the same results."""
+    monkeypatch.setenv("LZ4E_B200_SPARSE_SRC", sparse)
+    monkeypatch.setenv("LZ4E_B200_CHUNK_MB", "1")
+    rng = np.random.default_rng(33)
+    sizes = [4096] * 700 + [int(rng.integers(0, 30000)) for _ in range(60)]
+    datas = [common.synth(n, i & 3, 40 + i) for i, n in enumerate(sizes)]
+    specs = [sg.segs_random(n, rng, max_segs=5) for n in sizes]
+    dspecs = [dict(sg.segs_single(sg.compress_bound(n)), gap=0) for n in sizes]
+    ospecs = [sg.segs_random(n, rng, max_segs=5) for n in sizes]
+    _batch_roundtrip(ctx, ref_lib, datas, specs, dspecs, ospecs, _arena(ctx), _arena(ctx),
+                     _arena(ctx))
+
+
+def test_batch_sparse_sources_kernel_path(ctx, ref_lib, monkeypatch):
+    """64 KiB blocks over 16 odd segments with guard pages in between: neither side is dense,
+    so sources go up and results come down through the transfer kernel only."""
+    monkeypatch.setenv("LZ4E_B200_CHUNK_MB", "1")
+    monkeypatch.setenv("LZ4E_B200_SPARSE_SRC", "kernel")
+    n = 40
+    datas = [common.synth(65536, b & 3, 500 + b) for b in range(n)]
+    specs = [sg.segs_odd(65536, 16, b) for b in range(n)]
+    dspecs = [sg.segs_odd(sg.compress_bound(65536), 16, b + 7) for b in range(n)]
+    ospecs = [sg.segs_odd(65536, 16, b + 3) for b in range(n)]
+    ctx.sync()
+    h0, d0 = ctx.traffic()
+    rets = _batch_roundtrip(ctx, ref_lib, datas, specs, dspecs, ospecs, _arena(ctx), _arena(ctx),
+                            _arena(ctx))
+    ctx.sync()
+    h1, d1 = ctx.traffic()
+    moved = n * 65536 + int(rets.sum())
+    assert moved <= h1 - h0 <= moved + (1 << 20)
+    assert moved <= d1 - d0 <= moved + (1 << 20)
+
+
+def test_contexts_in_threads_and_destroy(ref_lib):
+    """Per-context workspaces: two contexts on the same device run batches from two threads at
+    once; destroying one (with its arenas) leaves the other usable, and a context created
+    afterwards starts from a clean workspace."""
+    import threading
+    n = 800
+    datas = [common.synth(4096, b & 3, 900 + b) for b in range(n)]
+    specs = [dict(sg.segs_single(4096), gap=0)] * n
+    dspecs = [dict(sg.segs_single(sg.compress_bound(4096)), gap=0)] * n
+    want = None
+    errs = []
+
+    def work(c, reps):
+        try:
+            for _ in range(reps):
+                src = common.build_layout(_arena(c), specs, datas)
+                dst = common.build_layout(_arena(c), dspecs)
+                creqs, keep = pkg.make_reqs(src, dst)
+                assert c.compress_batch(creqs, flags=pkg.F_KEEP_ITERS) == 0, c.err()
+                got = [bytes(dst.read_block(b, creqs["ret"][b])) for b in range(0, n, 37)]
+                assert got == want
+        except Exception as e:  # noqa: BLE001
+            errs.append(repr(e))
+
+    c0 = pkg.Context(0)
+    src = common.build_layout(_arena(c0), specs, datas)
+    ref_dst, (ref_rets, _) = common.oracle_compress(ref_lib, src, dspecs)
+    want = [bytes(ref_dst.read_block(b, ref_rets[b])) for b in range(0, n, 37)]
+    c1 = pkg.Context(0)
+    ts = [threading.Thread(target=work, args=(c, 3)) for c in (c0, c1)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
+    c0.close()  # its arenas and workspace go with it
+    work(c1, 1)
+    c2 = pkg.Context(0)
+    work(c2, 1)
+    assert not errs, errs
+    c1.close()
+    c2.close()
