@@ -352,8 +352,19 @@ def run_ours(args):
         cfg3 = run_cfg3(torch, pkg, ctx, stream, args, dist, rank, world, local)
         if rank == 0:
             result["extra"] = {"cfg3_64k": cfg3}
-    if rank == 0 and world == 1 and not args.no_extra and not args.no_replay:
-        result["extra"]["cfg5_replay"] = run_replay()
+    if not args.no_extra and not args.no_replay:
+        # configs[4]: one replay harness per GPU (its own process, its own request stream),
+        # started together; GB/s add up, latencies are the worst rank's
+        if dist is not None:
+            dist.barrier()
+        rep = run_replay(device=local, seed=1 + rank)
+        if dist is not None:
+            allrep = [None] * world
+            dist.all_gather_object(allrep, rep)
+        else:
+            allrep = [rep]
+        if rank == 0:
+            result["extra"]["cfg5_replay"] = merge_replay(allrep)
     if not args.no_e2e:
         e2e = run_e2e(torch, pkg, ctx, args, dist, rank, world, local)
         if rank == 0:
@@ -385,7 +396,30 @@ def profile_traffic(kernel):
     return None
 
 
-def run_replay():
+def merge_replay(reps):
+    """Aggregate of the per-GPU replay lines: throughput and counters add up, batch latencies
+    are the slowest rank's, every rank must have matched the oracle."""
+    bad = [r for r in reps if "error" in r]
+    if bad:
+        return {"error": bad[0]["error"], "n_gpus": len(reps)}
+    out = dict(reps[0])
+    out["n_gpus"] = len(reps)
+    if len(reps) == 1:
+        return out
+    for k in ("gbs", "write_gbs"):
+        out[k] = round(sum(r[k] for r in reps), 3)
+    for k in ("batch_ms_p50", "batch_ms_p99", "batch_ms_max"):
+        out[k] = max(r[k] for r in reps)
+    for k in ("write_reqs", "read_reqs", "write_bytes", "read_bytes", "compressed_bytes",
+              "oracle_compressed_bytes", "failed", "mismatches", "gpu_launches"):
+        out[k] = sum(r[k] for r in reps)
+    out["per_bio_digest_equal"] = all(r.get("per_bio_digest_equal") for r in reps)
+    out["per_gpu_gbs"] = [r["gbs"] for r in reps]
+    out["workload"] += " (one harness process per GPU, different request streams)"
+    return out
+
+
+def run_replay(device=0, seed=1):
     """BASELINE.json configs[4]: the C replay harness of the chunk layer / request path
     (tools/replay/lz4e_replay.c), QD256 random 4-128 KiB writes/reads on this GPU; --oracle
     makes it compare every bio's compressed bytes with the reference (checker, untimed)."""
@@ -394,7 +428,7 @@ def run_replay():
     try:
         if not os.path.exists(exe):
             subprocess.run(["make", "-C", os.path.dirname(exe)], check=True, capture_output=True)
-        cmd = [exe, "--arena-bios", "--batches", "48"]
+        cmd = [exe, "--arena-bios", "--batches", "48", "--device", str(device), "--seed", str(seed)]
         for so in (os.path.join(ROOT, "oracle", "_ref", "liblz4e_ref.so"),
                    os.path.join(ROOT, "oracle", "_build", "liblz4e_port.so")):
             if os.path.exists(so):

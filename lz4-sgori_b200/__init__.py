@@ -17,7 +17,7 @@ from . import sg  # noqa: F401  (re-exported helpers)
 from .sg import BIO_VEC, BVEC_ITER, PAGE_SIZE, compress_bound  # noqa: F401
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "liblz4e_b200.so")
+LIB_PATH = os.environ.get("LZ4E_B200_LIB") or os.path.join(HERE, "liblz4e_b200.so")
 
 DEV_BVEC = np.dtype([("addr", "<u8"), ("len", "<u4"), ("rsvd", "<u4")])
 DEV_ITER = np.dtype([("first", "<u4"), ("bi_size", "<u4"), ("bi_idx", "<u4"),

@@ -59,6 +59,7 @@ struct lz4e_b200_ctx {
 	int dvariant; /* LZ4E_DV_*: which decoder; -1 auto */
 	int dorder;   /* cost-ordered work queue from this many blocks on; 0 = never */
 	int wave_min; /* blocks above 8 KiB: wave decoder from this many blocks on */
+	int tma;      /* compress: TMA bulk staging of the input (shared-memory kernels) */
 	/* bytes moved between host and device through this context: copy engine
 	 * (host counters) and lz4e_xfer_kernel (device counters d_moved[0..1]) */
 	std::atomic<uint64_t> h2d_bytes, d2h_bytes;
@@ -154,6 +155,9 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 	ctx->dvariant = -1;
 	if (const char *e = getenv("LZ4E_B200_DVARIANT"))
 		ctx->dvariant = atoi(e);
+	ctx->tma = 0;
+	if (const char *e = getenv("LZ4E_B200_TMA"))
+		ctx->tma = atoi(e) ? 1 : 0;
 	ctx->wave_min = 0;
 	if (const char *e = getenv("LZ4E_B200_WAVE_MIN"))
 		ctx->wave_min = atoi(e);
@@ -247,6 +251,8 @@ int lz4e_b200_ctx_tune(lz4e_b200_ctx *ctx, const char *key, int value)
 		ctx->dorder = value;
 	else if (!strcmp(key, "wave_min"))
 		ctx->wave_min = value;
+	else if (!strcmp(key, "tma"))
+		ctx->tma = value ? 1 : 0;
 	else if (!strcmp(key, "gin_min"))
 		ctx->gin_min = value;
 	else if (!strcmp(key, "gin_per_sm"))
@@ -603,6 +609,7 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 	a.work_counter = next_counter(ctx, s);
 	a.faults = ctx->d_ctl + CTL_FAULTS;
 	a.nblocks = nblocks;
+	a.tma = (uint32_t)ctx->tma;
 	a.table_bytes = (flags & LZ4E_B200_DEV_NO_BYU16) ? 8192u : 16384u;
 	if (max_in_bytes > 65536u) /* 32-bit positions: 4096 entries of 4 bytes */
 		a.table_bytes = 16384u;

@@ -44,6 +44,7 @@
 #define LZ4E_K_MAX_INPUT 0x7E000000u /* lz4e.h:24 */
 #define LZ4E_K_TABLE_BYTES 16384u    /* LZ4E_MEMORY_USAGE 14, lz4e.h:11 */
 #define LZ4E_K_PAD 48u		     /* slack after each staging area */
+#define LZ4E_K_BAR 16u		     /* the warp's mbarrier (TMA staging of the input) */
 
 #define LZ4E_FAULT_RANGE 1u /* a block exceeded the limits given at launch */
 
@@ -72,13 +73,17 @@ struct lz4e_compress_args {
 	 * memory stride from one warp's area to the next */
 	uint32_t warps;
 	uint32_t warp_smem;
+	/* shared-memory kernels: stage congruent segments with 1-D TMA bulk copies
+	 * (cp.async.bulk + mbarrier) instead of loads/stores by the lanes */
+	uint32_t tma;
 };
 
 /* shared memory needed by one warp (in_cap = 0 for the GIN kernels) */
 static inline uint32_t lz4e_compress_smem_bytes(uint32_t table_bytes,
 						uint32_t in_cap, uint32_t out_cap)
 {
-	return table_bytes + (in_cap ? in_cap + LZ4E_K_PAD : 0u) + out_cap + LZ4E_K_PAD;
+	return table_bytes + (in_cap ? in_cap + LZ4E_K_PAD : 0u) + out_cap + LZ4E_K_PAD +
+	       LZ4E_K_BAR;
 }
 
 /* number of bytes advanced after k search visits: visit k uses step 1 for
@@ -227,12 +232,12 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 		}
 
 		if (n >= 13) {
-			/* zero the table: (1 << hashLog) entries of TABT (16-bit
-			 * positions up to 64 KiB, 32-bit ones above) */
+			/* the table — (1 << hashLog) entries of TABT, 16-bit positions
+			 * up to 64 KiB, 32-bit ones above — was zeroed by the caller
+			 * while the block's bytes were still in flight */
 			const uint32_t tbytes = (TT == LZ4E_TT_U16   ? 8192u
 						 : TT == LZ4E_TT_U32 ? 4096u
 								     : 2048u) * (uint32_t)sizeof(TABT);
-			const lz4e_u128 z = { 0, 0, 0, 0 };
 
 			if (tbytes > a.table_bytes) {
 				/* launched for byU32-only batches, block wants byU16 */
@@ -240,10 +245,6 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
 				return 0;
 			}
-
-			for (uint32_t i = lane * 16u; i < tbytes; i += 512u)
-				lz4e_st128(sm + i, z);
-			lz4e_syncwarp(LZ4E_FULL); /* table + gathered input visible */
 
 			/* first byte (:280-282): table[hash(0)] = 0 is a no-op on a
 			 * zeroed table of positions; search starts at 1 */
@@ -635,9 +636,10 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
  * Compress block b.  sm points at this warp's shared memory
  * (lz4e_compress_smem_bytes()).  All 32 lanes call it together.
  */
-template <bool DIRECT, bool GIN>
+template <bool DIRECT, bool GIN, bool TMA>
 LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
-				  uint8_t *sm, uint32_t lane, uint32_t slot)
+				  uint8_t *sm, uint32_t lane, uint32_t slot,
+				  uint64_t *bar, uint32_t &phase)
 {
 	const struct lz4e_b200_dev_iter si = a.src_iters[b];
 	const struct lz4e_b200_dev_iter di = a.dst_iters[b];
@@ -669,17 +671,33 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 		}
 	}
 
-	/* ---- gather + address mode (lz4e_compress.c:184-211) ---- */
+	/*
+	 * ---- gather + address mode (lz4e_compress.c:184-211) ----
+	 * Shared-memory kernels: every segment whose address is congruent mod 16
+	 * with its place in the staging area goes through the SM's TMA unit (1-D
+	 * cp.async.bulk, 16-byte aligned body; head and tail bytes by the lanes);
+	 * the copies are issued by lane 0, the warp zeroes its hash table while
+	 * they are in flight and then waits on the mbarrier.  Segments that are
+	 * not congruent (odd offsets behind the first one) are moved by the lanes
+	 * with funnel-shifted words as before.
+	 */
 	{
 		const struct lz4e_b200_dev_bvec *v =
 			a.src_bvecs + si.first + si.bi_idx;
 		uint32_t done_in = si.bi_bvec_done, rem = n, pos = 0, i = 0;
 		bool too_many = false;
+		bool bulk = false;
+
+		(void)bulk;
 		uint8_t *dbase = in_area;
 
 		if (n)
 			dbase += (uint32_t)(v->addr + done_in) & 15u;
 		d = dbase;
+#if defined(LZ4E_HAVE_TMA)
+		if (TMA && lane == 0)
+			lz4e_fence_async_smem(); /* the previous block's reads are done */
+#endif
 		while (rem) {
 			if (i >= BIO_MAX_VECS) {
 				too_many = true;
@@ -696,15 +714,55 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 				tt |= LZ4E_TT_U64;
 			if (take > rem)
 				take = rem;
-			lz4e_copy<32>(dbase + pos, g, take, lane);
+#if defined(LZ4E_HAVE_TMA)
+			if (TMA && take >= 256u &&
+			    ((((uint32_t)(uintptr_t)g) ^ lz4e_smem_addr(dbase + pos)) & 15u) == 0) {
+				const uint32_t head = (uint32_t)(-(uintptr_t)g) & 15u;
+				const uint32_t body = (take - head) & ~15u;
+				const uint32_t tail = take - head - body;
+				uint8_t *o = dbase + pos;
+
+				if (lane == 0) {
+					lz4e_mbar_expect(bar, body);
+					lz4e_tma_load(o + head, g + head, body, bar);
+				}
+				if (lane < head)
+					o[lane] = g[lane];
+				if (lane < tail)
+					o[head + body + lane] = g[head + body + lane];
+				bulk = true;
+			} else
+#endif
+				lz4e_copy<32>(dbase + pos, g, take, lane);
 			pos += take;
 			rem -= take;
 			done_in = 0;
 			i++;
 		}
+#if defined(LZ4E_HAVE_TMA)
+		if (TMA && bulk && lane == 0)
+			lz4e_mbar_arrive(bar);
+#endif
+		if (!(too_many && n >= 13) && n >= 13) {
+			/* zero the table while the bulk copies land */
+			const uint32_t tbytes =
+				(tt == LZ4E_TT_U16 ? 8192u : tt == LZ4E_TT_U32 ? 4096u : 2048u) *
+				(n > 65536u ? 4u : 2u);
+			const lz4e_u128 z = { 0, 0, 0, 0 };
+
+			if (tbytes <= a.table_bytes)
+				for (uint32_t k = lane * 16u; k < tbytes; k += 512u)
+					lz4e_st128(sm + k, z);
+		}
+#if defined(LZ4E_HAVE_TMA)
+		if (TMA && bulk) {
+			lz4e_mbar_wait(bar, phase);
+			phase ^= 1u;
+		}
+#endif
 		if (too_many && n >= 13) /* :268-277 */
 			goto done;
-		lz4e_syncwarp(LZ4E_FULL); /* gathered bytes visible to all lanes */
+		lz4e_syncwarp(LZ4E_FULL); /* gathered bytes and table visible to all lanes */
 	}
 
 	if (n > 65536u) {
@@ -750,10 +808,19 @@ done:
 }
 
 /* persistent loop: warps pull block indices from a global counter */
-template <bool DIRECT, bool GIN>
+template <bool DIRECT, bool GIN, bool TMA = false>
 LZ4E_DEV void lz4e_compress_warp(const lz4e_compress_args &a, uint8_t *sm,
 				 uint32_t lane, uint32_t slot)
 {
+	/* the warp's mbarrier sits at the end of its shared-memory area */
+	uint64_t *bar = reinterpret_cast<uint64_t *>(sm + a.warp_smem - LZ4E_K_BAR);
+	uint32_t phase = 0;
+
+#if defined(LZ4E_HAVE_TMA)
+	if (TMA && lane == 0)
+		lz4e_mbar_init(bar, 1);
+	lz4e_syncwarp(LZ4E_FULL);
+#endif
 	for (;;) {
 		uint32_t b = 0;
 
@@ -762,7 +829,7 @@ LZ4E_DEV void lz4e_compress_warp(const lz4e_compress_args &a, uint8_t *sm,
 		b = lz4e_shfl(LZ4E_FULL, b, 0);
 		if (b >= a.nblocks)
 			break;
-		lz4e_compress_block<DIRECT, GIN>(a, b, sm, lane, slot);
+		lz4e_compress_block<DIRECT, GIN, TMA>(a, b, sm, lane, slot, bar, phase);
 	}
 }
 

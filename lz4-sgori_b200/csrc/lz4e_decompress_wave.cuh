@@ -49,6 +49,7 @@
 #define LZ4E_W_LITMAX 256u /* literal runs of a regular sequence: below this */
 #define LZ4E_W_TMAX 2048u  /* output bytes of one wave */
 #define LZ4E_W_BIAS 4096u  /* keeps "compressed - output position" positive */
+#define LZ4E_W_RING 4096u  /* most recent output bytes kept in shared memory */
 
 /* per-warp shared memory */
 struct lz4e_wave_smem {
@@ -57,6 +58,15 @@ struct lz4e_wave_smem {
 	uint32_t qy[LZ4E_W_QCAP]; /* offset (16) | match length (16) */
 	uint32_t bm[LZ4E_W_TMAX / 32u]; /* first bytes of the wave's segments */
 	uint32_t seg[64];		 /* one word per segment */
+	/*
+	 * The last LZ4E_W_RING output bytes of the regular stretch, at index
+	 * (output position mod LZ4E_W_RING).  A match byte whose source is that
+	 * close is read from here instead of from the destination in global
+	 * memory: just-written output is not in L1 (stores write through and
+	 * invalidate), so every such read was an L2 round trip — the decoder's
+	 * largest stall — and, for scattered destinations, a segment lookup.
+	 */
+	uint8_t ring[LZ4E_W_RING];
 };
 
 LZ4E_DEV uint64_t lz4e_w_shfl_ptr(const void *p, int src)
@@ -80,6 +90,11 @@ LZ4E_DEV void lz4e_w_hot(lz4e_gstate<32, false> &g, lz4e_wave_smem *ws, uint32_t
 	uint32_t ip = g.ip, op = g.op;
 	uint32_t qh = 0, qn = 0;
 	bool stop = false;
+	/* the ring holds output positions [max(ring_lo, front - RING), front):
+	 * what was produced before this call (by-the-book sequences, the previous
+	 * block) is not in it */
+	const uint32_t ring_lo = op;
+	uint8_t *ring = ws->ring;
 
 	LZ4E_ASSUME_GLOBAL(inb);
 	LZ4E_ASSUME_GLOBAL(ob);
@@ -260,28 +275,44 @@ LZ4E_DEV void lz4e_w_hot(lz4e_gstate<32, false> &g, lz4e_wave_smem *ws, uint32_t
 					}
 				}
 				const uint32_t pos = op + (uint32_t)sp; /* match: linear output position */
-				const uint8_t *src = isl ? inb + (uint32_t)sp : ob + pos;
+				/* this step overwrites ring positions front - RING ..
+				 * front - RING + 31: sources that old go to memory */
+				const uint32_t front = op + c0;
+				const bool near = on && !isl && pos >= ring_lo &&
+						  front - pos <= LZ4E_W_RING - 32u;
+				const bool far = on && !near;
+				uint32_t v = 0;
 
-				if (nseg > 1u) {
-					const bool back = on && !isl && pos < o_lo;
+				if (near)
+					v = ring[pos & (LZ4E_W_RING - 1u)];
+				if (lz4e_ballot(LZ4E_FULL, far)) {
+					const uint8_t *src = isl ? inb + (uint32_t)sp : ob + pos;
 
-					if (lz4e_ballot(LZ4E_FULL, back)) {
-						if (back) {
-							if (pos >= p_lo) {
-								src = pb + pos;
-							} else {
-								uint32_t k = oseg - 1u;
+					if (nseg > 1u) {
+						const bool back = far && !isl && pos < o_lo;
 
-								while (m->start[k] > pos)
-									k--;
-								src = (const uint8_t *)(uintptr_t)m->bias[k] + pos;
+						if (lz4e_ballot(LZ4E_FULL, back)) {
+							if (back) {
+								if (pos >= p_lo) {
+									src = pb + pos;
+								} else {
+									uint32_t k = oseg - 1u;
+
+									while (m->start[k] > pos)
+										k--;
+									src = (const uint8_t *)(uintptr_t)m->bias[k] + pos;
+								}
 							}
 						}
 					}
+					LZ4E_ASSUME_GLOBAL(src);
+					if (far)
+						v = *src;
 				}
-				LZ4E_ASSUME_GLOBAL(src);
-				if (on)
-					ob[op + j] = *src;
+				if (on) {
+					ob[op + j] = (uint8_t)v;
+					ring[(op + j) & (LZ4E_W_RING - 1u)] = (uint8_t)v;
+				}
 				base += (uint32_t)lz4e_popc(w);
 				lz4e_syncwarp(LZ4E_FULL);
 			}

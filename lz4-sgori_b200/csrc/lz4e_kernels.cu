@@ -17,14 +17,14 @@ extern __shared__ __align__(16) uint8_t lz4e_smem[];
 /* ---- K2: compression, one warp per block in flight; a.warps warps per CTA,
  * each with its own a.warp_smem bytes of shared memory ---------------------- */
 #define LZ4E_C_MAX_WARPS 24
-template <bool DIRECT, bool GIN>
+template <bool DIRECT, bool GIN, bool TMA = false>
 __global__ void __launch_bounds__(LZ4E_C_MAX_WARPS * 32)
 lz4e_compress_kernel(const lz4e_compress_args a)
 {
 	const uint32_t w = threadIdx.x >> 5;
 
-	lz4e_compress_warp<DIRECT, GIN>(a, lz4e_smem + (size_t)w * a.warp_smem, threadIdx.x & 31,
-					blockIdx.x * a.warps + w);
+	lz4e_compress_warp<DIRECT, GIN, TMA>(a, lz4e_smem + (size_t)w * a.warp_smem,
+					     threadIdx.x & 31, blockIdx.x * a.warps + w);
 }
 
 /* ---- K4: decompression, LZ4E_D_WARPS warps per CTA, 32/GS blocks per warp */
@@ -92,8 +92,14 @@ static int lz4e_set_smem(const void *fn, size_t bytes)
 
 typedef void (*lz4e_compress_fn)(const lz4e_compress_args);
 
-static lz4e_compress_fn compress_fn(int direct, int gin)
+/* tma: the shared-memory kernels with 1-D TMA bulk staging of the input (its
+ * own instantiation: merely compiling the cp.async.bulk / mbarrier path into
+ * the plain kernel costs it 10 %, profiles/r2o_tma_staging.md) */
+static lz4e_compress_fn compress_fn(int direct, int gin, int tma = 0)
 {
+	if (!gin && tma)
+		return direct ? lz4e_compress_kernel<true, false, true>
+			      : lz4e_compress_kernel<false, false, true>;
 	if (gin)
 		return direct ? lz4e_compress_kernel<true, true> : lz4e_compress_kernel<false, true>;
 	return direct ? lz4e_compress_kernel<true, false> : lz4e_compress_kernel<false, false>;
@@ -111,7 +117,7 @@ int lz4e_compress_plan(lz4e_compress_args *a, int direct, int gin, int sm_count,
 {
 	size_t smem = lz4e_compress_smem_bytes(a->table_bytes, gin ? 0u : a->in_cap, a->out_cap);
 	int per_sm = 0;
-	lz4e_compress_fn fn = compress_fn(direct, gin);
+	lz4e_compress_fn fn = compress_fn(direct, gin, (int)a->tma);
 
 	smem = (smem + 15) & ~(size_t)15;
 	a->warps = 1;
@@ -170,7 +176,7 @@ int lz4e_compress_plan(lz4e_compress_args *a, int direct, int gin, int sm_count,
 int lz4e_launch_compress(const lz4e_compress_args *a, int direct, int gin, int grid,
 			 size_t smem, cudaStream_t stream)
 {
-	lz4e_compress_fn fn = compress_fn(direct, gin);
+	lz4e_compress_fn fn = compress_fn(direct, gin, (int)a->tma);
 
 	fn<<<(unsigned)grid, 32u * a->warps, smem, stream>>>(*a);
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;

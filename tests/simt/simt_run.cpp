@@ -235,6 +235,9 @@ int simt_compress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 	a.out_cap = out_cap;
 	a.in_scratch = gin ? slot.data() : nullptr;
 	a.in_stride = gin ? in_cap + 256 : 0;
+	a.warps = 1;
+	a.warp_smem = (bytes + 15u) & ~15u;
+	a.tma = 0;
 	uint8_t *sm = (uint8_t *)smraw;
 
 	/* out_cap 64 = what lz4e_b200_compress_dev passes for linear destinations:

@@ -16,7 +16,7 @@ pytestmark = pytest.mark.gpu
 # 2 = pipelined group decoder, 1 = group decoder, 0/8 = round-1 group decoder
 DECODERS = [(0, 1), (3, 32), (2, 8), (2, 16), (1, 8), (0, 8)]
 DEFAULTS = {"dvariant": -1, "dgroup": 0, "dstage": -1, "dorder": 2048, "gin_small": 2,
-            "gin_min": 12288}
+            "gin_min": 12288, "tma": 0}
 
 
 @pytest.fixture
@@ -107,3 +107,17 @@ def test_limited_output_64k(ctx, ref_lib, tuned, gin_small):
         _, _, rets = P._check_compress(ctx, ref_lib, datas, specs, dspecs, flags=flags,
                                        check_untouched=False)
         assert (rets[0::5] == sizes).all() and (rets[1::5] == 0).all()
+
+
+def test_tma_staged_input_parity(ctx, ref_lib, tuned):
+    """north_star's "per-page 1-D TMA bulk staging": with tma=1 the shared-memory compress
+    kernels bring every 16-byte-congruent segment in with cp.async.bulk + mbarrier (heads, tails
+    and incongruent segments by the lanes).  Same bytes as the reference on aligned pages, page
+    bvecs, odd segments and fuzzed layouts."""
+    tuned(tma=1)
+    P.test_config2_4k_mixed(ctx, ref_lib)
+    P.test_64k_page_bvecs_byu16(ctx, ref_lib)
+    P.test_config3_64k_odd_segments(ctx, ref_lib)
+    P.test_fuzz_segmentations_and_sizes(ctx, ref_lib)
+    P.test_limited_output(ctx, ref_lib)
+    P.test_survey_sanity_values(ctx, ref_lib)
