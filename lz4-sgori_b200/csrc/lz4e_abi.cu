@@ -679,6 +679,21 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 				return LZ4E_B200_ENOMEM;
 			}
 		}
+		/* bios of very different sizes (configs[4]: 4-128 KiB): hand the
+		 * large ones out first, or the batch ends with one warp working on
+		 * a 128 KiB block it took last while the machine idles */
+		a.order = nullptr;
+		if (max_in_bytes > 8192u && nblocks >= 32u && ctx->dorder > 0) {
+			uint32_t *ord = (uint32_t *)stream_scratch(
+				ctx, s, SCRATCH_ORDER,
+				((size_t)nblocks + 2 * LZ4E_ORDER_BUCKETS) * sizeof(uint32_t));
+
+			if (ord && !lz4e_launch_order(src_iters, nullptr, nblocks, ord + nblocks, ord, s,
+						       max_in_bytes + 1u)) {
+				a.order = ord;
+				ctx->launches += 2;
+			}
+		}
 		if (lz4e_launch_compress(&a, direct, gin, grid, smem, s)) {
 			set_err(ctx, "compress launch failed: %s",
 				cudaGetErrorString(cudaGetLastError()));

@@ -58,6 +58,7 @@ struct lz4e_compress_args {
 	int32_t *rets;
 	struct lz4e_b200_dev_end *ends; /* may be NULL */
 	uint32_t *work_counter;		/* zeroed before launch */
+	const uint32_t *order;		/* optional: block indices, most expensive first */
 	uint32_t *faults;
 	uint32_t nblocks;
 	uint32_t table_bytes; /* 16384, or 8192 when no block can select byU16 */
@@ -212,7 +213,9 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 		const uint32_t matchlimit = n - 5u;
 		/* the whole output fits the staging area: one flush at the end */
 		const bool whole = DIRECT || a.out_cap >= (cap < n + n / 255u + 16u ? cap : n + n / 255u + 16u);
-		const bool fast_ok = whole && !limited;
+		/* streaming output (a window smaller than the block's bound) takes the
+		 * fast chain too: the window is flushed when four more bytes do not fit */
+		const bool fast_ok = !limited;
 		uint32_t anchor = 0, op = 0;
 		lz4e_out_stage st;
 
@@ -365,6 +368,9 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					const uint32_t ml = (uint32_t)lz4e_ffs(fnz) - 1u;
 					const uint32_t na = fip + ml;
 					const uint32_t off = ip - mp;
+
+					if (!whole && op - st.win + 4u > st.cap)
+						lz4e_stage_flush(st, op, a.out_cap, lane);
 					uint8_t *o = st.cur0 + (op - st.win);
 					const bool last = na > mflimit; /* :456 */
 
@@ -829,6 +835,8 @@ LZ4E_DEV void lz4e_compress_warp(const lz4e_compress_args &a, uint8_t *sm,
 		b = lz4e_shfl(LZ4E_FULL, b, 0);
 		if (b >= a.nblocks)
 			break;
+		if (a.order)
+			b = a.order[b];
 		lz4e_compress_block<DIRECT, GIN, TMA>(a, b, sm, lane, slot, bar, phase);
 	}
 }

@@ -34,7 +34,9 @@ int lz4e_launch_decompress(const lz4e_decompress_args *a, int group, int stage,
 #define LZ4E_ORDER_BUCKETS 64u
 int lz4e_launch_order(const struct lz4e_b200_dev_iter *src_iters,
 		      const struct lz4e_b200_dev_iter *dst_iters, uint32_t n, uint32_t *ctl,
-		      uint32_t *order, cudaStream_t stream);
+		      uint32_t *order, cudaStream_t stream, uint32_t by_size = 0);
+/* by_size != 0: order by source size alone (largest first, by_size = the
+ * largest size + 1): the compressor's cost estimate; dst_iters is not read */
 
 
 /* exact-byte host <-> device transfers by the SMs (lz4e_xfer.cu) */

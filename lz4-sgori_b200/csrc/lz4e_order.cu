@@ -25,9 +25,18 @@
 #define ORDER_THREADS 256u
 
 static __device__ __forceinline__ uint32_t order_key(const struct lz4e_b200_dev_iter &s,
-						     const struct lz4e_b200_dev_iter &d)
+						     const struct lz4e_b200_dev_iter *dp,
+						     uint32_t b, uint32_t by_size)
 {
-	const uint32_t c = s.bi_size, cap = d.bi_size;
+	const uint32_t c = s.bi_size;
+
+	if (by_size) {
+		/* compression: cost follows the input size; largest first */
+		const uint32_t k = (uint32_t)(((uint64_t)c * (LZ4E_ORDER_BUCKETS - 1u)) / by_size);
+
+		return LZ4E_ORDER_BUCKETS - 1u - (k < LZ4E_ORDER_BUCKETS ? k : LZ4E_ORDER_BUCKETS - 1u);
+	}
+	const uint32_t cap = dp[b].bi_size;
 
 	if (cap == 0 || c >= cap)
 		return LZ4E_ORDER_BUCKETS - 1u; /* incompressible or malformed: cheap */
@@ -37,7 +46,8 @@ static __device__ __forceinline__ uint32_t order_key(const struct lz4e_b200_dev_
 
 __global__ void __launch_bounds__(ORDER_THREADS)
 lz4e_order_count_kernel(const struct lz4e_b200_dev_iter *src_iters,
-			const struct lz4e_b200_dev_iter *dst_iters, uint32_t n, uint32_t *hist)
+			const struct lz4e_b200_dev_iter *dst_iters, uint32_t n, uint32_t *hist,
+			uint32_t by_size)
 {
 	__shared__ uint32_t h[LZ4E_ORDER_BUCKETS];
 
@@ -50,7 +60,7 @@ lz4e_order_count_kernel(const struct lz4e_b200_dev_iter *src_iters,
 		const uint32_t b = base + i;
 
 		if (b < n)
-			atomicAdd(&h[order_key(src_iters[b], dst_iters[b])], 1u);
+			atomicAdd(&h[order_key(src_iters[b], dst_iters, b, by_size)], 1u);
 	}
 	__syncthreads();
 	if (threadIdx.x < LZ4E_ORDER_BUCKETS && h[threadIdx.x])
@@ -60,7 +70,7 @@ lz4e_order_count_kernel(const struct lz4e_b200_dev_iter *src_iters,
 __global__ void __launch_bounds__(ORDER_THREADS)
 lz4e_order_place_kernel(const struct lz4e_b200_dev_iter *src_iters,
 			const struct lz4e_b200_dev_iter *dst_iters, uint32_t n,
-			const uint32_t *hist, uint32_t *cursor, uint32_t *order)
+			const uint32_t *hist, uint32_t *cursor, uint32_t *order, uint32_t by_size)
 {
 	__shared__ uint32_t h[LZ4E_ORDER_BUCKETS];    /* this tile's counts */
 	__shared__ uint32_t at[LZ4E_ORDER_BUCKETS];   /* where this tile's bucket starts */
@@ -77,7 +87,7 @@ lz4e_order_place_kernel(const struct lz4e_b200_dev_iter *src_iters,
 		key[k] = 0;
 		rank[k] = 0;
 		if (b < n) {
-			key[k] = order_key(src_iters[b], dst_iters[b]);
+			key[k] = order_key(src_iters[b], dst_iters, b, by_size);
 			rank[k] = atomicAdd(&h[key[k]], 1u);
 		}
 	}
@@ -104,14 +114,15 @@ lz4e_order_place_kernel(const struct lz4e_b200_dev_iter *src_iters,
 /* ctl: 2 * LZ4E_ORDER_BUCKETS words of device memory (histogram + cursors) */
 int lz4e_launch_order(const struct lz4e_b200_dev_iter *src_iters,
 		      const struct lz4e_b200_dev_iter *dst_iters, uint32_t n, uint32_t *ctl,
-		      uint32_t *order, cudaStream_t stream)
+		      uint32_t *order, cudaStream_t stream, uint32_t by_size)
 {
 	const unsigned grid = (n + ORDER_TILE - 1u) / ORDER_TILE;
 
 	if (cudaMemsetAsync(ctl, 0, 2 * LZ4E_ORDER_BUCKETS * sizeof(uint32_t), stream) != cudaSuccess)
 		return -1;
-	lz4e_order_count_kernel<<<grid, ORDER_THREADS, 0, stream>>>(src_iters, dst_iters, n, ctl);
+	lz4e_order_count_kernel<<<grid, ORDER_THREADS, 0, stream>>>(src_iters, dst_iters, n, ctl,
+								    by_size);
 	lz4e_order_place_kernel<<<grid, ORDER_THREADS, 0, stream>>>(
-		src_iters, dst_iters, n, ctl, ctl + LZ4E_ORDER_BUCKETS, order);
+		src_iters, dst_iters, n, ctl, ctl + LZ4E_ORDER_BUCKETS, order, by_size);
 	return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

@@ -472,6 +472,9 @@ struct lz4e_dev *lz4e_dev_create(uint64_t capacity)
 		return NULL;
 	}
 	dev->capacity = capacity;
+	/* touch every page now: the stand-in device must not take page faults
+	 * inside the timed request path */
+	memset(dev->store, 0, capacity ? capacity : 1);
 	pthread_mutex_init(&dev->mu, NULL);
 	return dev;
 }

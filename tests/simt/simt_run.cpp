@@ -228,6 +228,7 @@ int simt_compress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 	a.rets = rets;
 	a.ends = ends;
 	a.work_counter = &counter;
+	a.order = nullptr;
 	a.faults = faults;
 	a.nblocks = nblocks;
 	a.table_bytes = table_bytes;
