@@ -169,8 +169,12 @@ LZ4E_DEV void lz4e_stage_flush(lz4e_out_stage &s, uint32_t op, uint32_t out_cap,
 LZ4E_DEV void lz4e_put_run(uint8_t *p, uint32_t count, uint32_t last,
 			   uint32_t lane)
 {
-	for (uint32_t i = lane; i < count; i += 32)
-		p[i] = (i + 1 == count) ? (uint8_t)last : (uint8_t)255;
+	/* almost always one or two bytes: a single predicated store */
+	if (lane < count)
+		p[lane] = (lane + 1u == count) ? (uint8_t)last : (uint8_t)255;
+	if (count > 32u)
+		for (uint32_t i = lane + 32u; i < count; i += 32)
+			p[i] = (i + 1 == count) ? (uint8_t)last : (uint8_t)255;
 }
 
 /*
@@ -190,6 +194,9 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 	const uint32_t cap = di.bi_size;
 	TABT *tab = reinterpret_cast<TABT *>(sm);
 	int32_t ret = 0;
+	/* 16-bit positions: the block is at most 64 KiB, so every candidate is
+	 * within LZ4E_DISTANCE_MAX (lz4e_compress.c:326-327 can never fire) */
+	constexpr bool NEAR = sizeof(TABT) == 2;
 
 	if (GIN)
 		LZ4E_ASSUME_GLOBAL(d);
@@ -291,7 +298,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 
 				if (lower)
 					m = mj;
-				if (valid && k != -2 && m + 65535u >= pos)
+				if (valid && k != -2 && (NEAR || m + 65535u >= pos))
 					ok = lz4e_sld32u(da, m + dm) == seq;
 
 				const uint32_t okmask = lz4e_ballot(LZ4E_FULL, ok);
@@ -360,7 +367,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					const uint32_t qm = qh2 == qh ? q - 2u : (uint32_t)tab[qh];
 					const bool fne = lane >= matchlimit - fip ||
 							 (sq & 0xffu) != d[mp + 4u + lane];
-					const bool qok = qm + 65535u >= q && lz4e_sld32u(da, qm + dm) == sq;
+					const bool qok = (NEAR || qm + 65535u >= q) && lz4e_sld32u(da, qm + dm) == sq;
 					const uint32_t fnz = lz4e_ballot(LZ4E_FULL, fne);
 
 					if (fnz == 0)
@@ -443,7 +450,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 						q_h = lz4e_hash(sq, b4q, TT);
 						q_h2 = lz4e_hash(sp, b4p, TT);
 						q_m = q_h2 == q_h ? q - 2u : (uint32_t)tab[q_h];
-						q_ok = q_m + 65535u >= q && lz4e_sld32u(da, q_m + dm) == sq;
+						q_ok = (NEAR || q_m + 65535u >= q) && lz4e_sld32u(da, q_m + dm) == sq;
 					}
 					if (lim) { /* uniform: 0 after an immediate match */
 						bool beq = false;

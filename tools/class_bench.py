@@ -22,19 +22,24 @@ def main():
     ctx = pkg.Context(0)
     d_src, d_dst, d_out = ctx.dev_alloc(n * 4096), ctx.dev_alloc(n * bench.DST_STRIDE), ctx.dev_alloc(n * 4096)
     (sbv, sit), (dbv, dit), (obv, oit) = bench.cfg2_tables(pkg, d_src, d_dst, d_out, n)
+    cflags = pkg.DEV_DST_LINEAR
+    if os.environ.get("CLASS_U32"):  # occupancy probe: raw bv_len > 4096 selects byU32 (8 KiB table)
+        sbv["len"] = 8192
+        cflags |= pkg.DEV_NO_BYU16
     t = [ctx.upload(x) for x in (sbv, sit, dbv, dit, obv, oit)]
     r1, r2 = ctx.dev_alloc(4 * n), ctx.dev_alloc(4 * n)
     host = np.zeros((n, 4096), dtype=np.uint8)
-    for cls in range(4):
+    only = os.environ.get("CLASS_ONLY")
+    for cls in ([int(only)] if only else range(4)):
         for b in range(n):
             lz4e_synth.lib().lz4e_synth_fill_host(host[b].ctypes.data, 4096, cls, 4 * b + cls)
         ctx.check(pkg.lib().lz4e_b200_copy_h2d(ctx.h, None, d_src, host.ctypes.data, n * 4096), "h2d")
         ctx.sync()
-        ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1, flags=pkg.DEV_DST_LINEAR)
+        ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1, flags=cflags)
         ctx.sync()
         t0 = time.perf_counter()
         for _ in range(reps):
-            ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1, flags=pkg.DEV_DST_LINEAR)
+            ctx.compress_dev(t[0], t[1], t[2], t[3], n, 4096, r1, flags=cflags)
         ctx.sync()
         tc = (time.perf_counter() - t0) / reps
         rets = ctx.download(r1, np.int32, n)
