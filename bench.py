@@ -543,6 +543,13 @@ def run_e2e(torch, pkg, ctx, args, dist=None, rank=0, world=1, local=0):
     the timed loop is bracketed by barriers and the slowest rank's time counts."""
     sg = pkg.sg
     nb = args.e2e_blocks
+    # How compressed blocks (40 % of their LZ4E_COMPRESSBOUND slots) go up for decompression:
+    # alone on the host a GPU is fastest with one copy-engine transfer of the spanned range
+    # (29.5 vs 33 ms per GiB); when several GPUs share the host's memory system the bytes count
+    # and the exact-byte transfer kernel wins (8 GPUs: 45.1 vs 39.8 GB/s,
+    # profiles/r2ab_e2e_n8.md).  The library's default is the former; set per deployment.
+    if world > 1:
+        os.environ.setdefault("LZ4E_B200_SPARSE_SRC", "kernel")
     src_arena = pkg.Arena(ctx, nb + 1)
     dst_pages = (nb * DST_STRIDE + 4095) // 4096 + 2
     dst_arena = pkg.Arena(ctx, dst_pages)
@@ -606,6 +613,7 @@ def run_e2e(torch, pkg, ctx, args, dist=None, rank=0, world=1, local=0):
         a.close()
     return {"value": round(world * nb * BLOCK / dt / 1e9, 3),
             "unit": UNIT, "buffers": "host (pinned page arenas); copies inside the timed region",
+            "sparse_src": os.environ.get("LZ4E_B200_SPARSE_SRC", "range when >= 25 % full (default)"),
             "algorithmic_pcie_bytes_per_step": int(2 * (nb * BLOCK + int(sizes.sum()))) * world,
             "blocks": world * nb, "ms_per_step": round(dt * 1e3, 3),
             "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
