@@ -23,6 +23,10 @@
 #define CTL_FAULTS CTL_COUNTERS
 #define CTL_WORDS (CTL_COUNTERS + 8)
 
+/* held while a *_dev call plans and enqueues its launch: kernel attributes
+ * (dynamic shared memory size) are per function and device, not per launch */
+static std::mutex g_launch_mu;
+
 struct lz4e_b200_arena {
 	lz4e_b200_ctx *ctx;
 	uint8_t *host;
@@ -59,6 +63,7 @@ struct lz4e_b200_ctx {
 	int dvariant; /* LZ4E_DV_*: which decoder; -1 auto */
 	int dorder;   /* cost-ordered work queue from this many blocks on; 0 = never */
 	int wave_min; /* blocks above 8 KiB: wave decoder from this many blocks on */
+	int wave_serial; /* wave decoder: sequence-serial copy from this many bytes per sequence */
 	int tma;      /* compress: TMA bulk staging of the input (shared-memory kernels) */
 	/* bytes moved between host and device through this context: copy engine
 	 * (host counters) and lz4e_xfer_kernel (device counters d_moved[0..1]) */
@@ -155,6 +160,9 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 	ctx->dvariant = -1;
 	if (const char *e = getenv("LZ4E_B200_DVARIANT"))
 		ctx->dvariant = atoi(e);
+	ctx->wave_serial = 32;
+	if (const char *e = getenv("LZ4E_B200_WAVE_SERIAL"))
+		ctx->wave_serial = atoi(e);
 	ctx->tma = 0;
 	if (const char *e = getenv("LZ4E_B200_TMA"))
 		ctx->tma = atoi(e) ? 1 : 0;
@@ -251,6 +259,8 @@ int lz4e_b200_ctx_tune(lz4e_b200_ctx *ctx, const char *key, int value)
 		ctx->dorder = value;
 	else if (!strcmp(key, "wave_min"))
 		ctx->wave_min = value;
+	else if (!strcmp(key, "wave_serial"))
+		ctx->wave_serial = value;
 	else if (!strcmp(key, "tma"))
 		ctx->tma = value ? 1 : 0;
 	else if (!strcmp(key, "gin_min"))
@@ -599,6 +609,7 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 		return LZ4E_B200_EINVAL;
 	}
 	cudaSetDevice(ctx->device);
+	std::lock_guard<std::mutex> launch_lock(g_launch_mu);
 	s = pick(ctx, stream);
 	a.src_bvecs = src_bvecs;
 	a.src_iters = src_iters;
@@ -776,6 +787,7 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 	else if (variant != LZ4E_DV_OLD && group != 4 && group != 8 && group != 16)
 		group = 8;
 	cudaSetDevice(ctx->device);
+	std::lock_guard<std::mutex> launch_lock(g_launch_mu);
 	s = pick(ctx, stream);
 	a.src_bvecs = src_bvecs;
 	a.src_iters = src_iters;
@@ -790,6 +802,7 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 	a.in_scratch = nullptr;
 	a.in_stride = 0;
 	a.order = nullptr;
+	a.wave_serial = ctx->wave_serial > 0 ? (uint32_t)ctx->wave_serial : 0u;
 	if (variant != LZ4E_DV_OLD || group == 1) {
 		/* hand the blocks out by decreasing estimated cost (lz4e_order.cu) */
 		if (ctx->dorder > 0 && nblocks >= (uint32_t)ctx->dorder) {

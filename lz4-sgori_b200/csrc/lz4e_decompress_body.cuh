@@ -59,6 +59,9 @@ struct lz4e_decompress_args {
 	/* work item i is block order[i] (cost-ordered queue, lz4e_order.cu);
 	 * NULL = batch order */
 	const uint32_t *order;
+	/* wave decoder: waves whose sequences average at least this many output
+	 * bytes are copied one sequence at a time (0: never) */
+	uint32_t wave_serial;
 };
 
 

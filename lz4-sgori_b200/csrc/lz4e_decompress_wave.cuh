@@ -74,11 +74,33 @@ LZ4E_DEV uint64_t lz4e_w_shfl_ptr(const void *p, int src)
 	return lz4e_shfl64((uint64_t)(uintptr_t)p, src);
 }
 
+/* address holding output byte `pos` (already written) of the current block */
+LZ4E_DEV const uint8_t *lz4e_w_outaddr(const lz4e_gstate<32, false> &g, const lz4e_omap *m,
+				       uint32_t pos)
+{
+	const uint8_t *src = g.ob + pos;
+
+	if (g.nseg > 1u && pos < g.o_lo) {
+		if (pos >= g.p_lo) {
+			src = g.pb + pos;
+		} else {
+			uint32_t k = g.oseg - 1u;
+
+			while (m->start[k] > pos)
+				k--;
+			src = (const uint8_t *)(uintptr_t)m->bias[k] + pos;
+		}
+	}
+	LZ4E_ASSUME_GLOBAL(src);
+	return src;
+}
+
 /*
  * Regular sequences of the current block until the next one is not regular.
  * On return g.ip / g.op name that sequence; everything before it is written.
  */
-LZ4E_DEV void lz4e_w_hot(lz4e_gstate<32, false> &g, lz4e_wave_smem *ws, uint32_t lane)
+LZ4E_DEV void lz4e_w_hot(lz4e_gstate<32, false> &g, lz4e_wave_smem *ws, uint32_t lane,
+			  uint32_t serial_min)
 {
 	const uint8_t *inb = g.inb;
 	uint8_t *ob = g.ob, *pb = g.pb;
@@ -199,6 +221,60 @@ LZ4E_DEV void lz4e_w_hot(lz4e_gstate<32, false> &g, lz4e_wave_smem *ws, uint32_t
 		const uint32_t T = na ? lz4e_shfl(LZ4E_FULL, incl, (int)(na - 1u)) : 0u;
 
 		/*
+		 * Long sequences (serial_min output bytes or more on average): one
+		 * sequence at a time, all lanes on its bytes, 32 per pass.  A pass
+		 * costs about a third of a byte-parallel step below and needs no
+		 * segment table; the byte-parallel form keeps every lane busy
+		 * whatever the lengths are and wins on short sequences (text:
+		 * 8 bytes per sequence).  Sources come from the ring when they are
+		 * close, and a match with an offset below 32 is its first period
+		 * repeated, so no pass reads what the same pass writes.
+		 */
+		if (na && serial_min && T >= serial_min * na) {
+			for (uint32_t q = 0; q < na; q++) {
+				const uint32_t sx = lz4e_shfl(LZ4E_FULL, dx, (int)q);
+				const uint32_t sy = lz4e_shfl(LZ4E_FULL, dy, (int)q);
+				const uint32_t o0 = op + lz4e_shfl(LZ4E_FULL, r, (int)q);
+				const uint32_t s_lp = sx & 0xffffffu, s_lit = sx >> 24;
+				const uint32_t s_off = sy & 0xffffu, s_ml = sy >> 16;
+				const uint32_t m0 = o0 + s_lit;
+
+				if (s_lit) {
+					for (uint32_t i = lane; i < s_lit; i += 32u) {
+						const uint8_t v = inb[s_lp + i];
+
+						ob[o0 + i] = v;
+						ring[(o0 + i) & (LZ4E_W_RING - 1u)] = v;
+					}
+					lz4e_syncwarp(LZ4E_FULL);
+				}
+				const float rc = lz4e_rcpf((float)s_off);
+
+				for (uint32_t c = 0; c < s_ml; c += 32u) {
+					const uint32_t i = c + lane;
+					/* offset below 32: byte i of the first period */
+					const uint32_t k =
+						s_off < 32u
+							? i - s_off * (uint32_t)(((float)i + 0.5f) * rc)
+							: i;
+					const uint32_t pos = m0 - s_off + k;
+					const uint32_t front = m0 + c;
+
+					if (i < s_ml) {
+						uint8_t v;
+
+						if (pos >= ring_lo && front - pos <= LZ4E_W_RING - 32u)
+							v = ring[pos & (LZ4E_W_RING - 1u)];
+						else
+							v = *lz4e_w_outaddr(g, m, pos);
+						ob[m0 + i] = v;
+						ring[(m0 + i) & (LZ4E_W_RING - 1u)] = v;
+					}
+					lz4e_syncwarp(LZ4E_FULL);
+				}
+			}
+		} else {
+		/*
 		 * Segment table of the wave: every literal run and every match is
 		 * one segment of the wave's T output bytes; bm has a bit for the
 		 * first byte of each, seg[] one word per segment in output order:
@@ -317,6 +393,7 @@ LZ4E_DEV void lz4e_w_hot(lz4e_gstate<32, false> &g, lz4e_wave_smem *ws, uint32_t
 				lz4e_syncwarp(LZ4E_FULL);
 			}
 		}
+		}
 		if (na) {
 			op += T;
 			qh = (qh + na) & (LZ4E_W_QCAP - 1u);
@@ -367,7 +444,7 @@ LZ4E_DEV void lz4e_decompress_wave(const lz4e_decompress_args &a, lz4e_wave_smem
 				continue;
 		}
 		lz4e_syncwarp(LZ4E_FULL);
-		lz4e_w_hot(g, ws, lane);
+		lz4e_w_hot(g, ws, lane, a.wave_serial);
 	}
 }
 

@@ -237,9 +237,15 @@ static void pack_run(struct workers *wk, const struct bounce *bn, size_t count, 
 	pthread_mutex_unlock(&wk->mu);
 }
 
-static void ws_dtor(lz4e_b200_ctx *ctx, void *p)
+#define NWS 2 /* batches in flight per context */
+
+/* what is attached to the context: NWS workspaces, handed out to batches */
+struct host_pool {
+	struct host_ws ws[NWS];
+};
+
+static void ws_release(lz4e_b200_ctx *ctx, struct host_ws *ws)
 {
-	struct host_ws *ws = p;
 	int l;
 
 	if (!ws->ready)
@@ -268,14 +274,19 @@ static void ws_dtor(lz4e_b200_ctx *ctx, void *p)
 	ws->ready = 0;
 }
 
-/* the context's workspace, created on first use; NULL when that fails */
-static struct host_ws *ws_get(lz4e_b200_ctx *ctx)
+static void ws_dtor(lz4e_b200_ctx *ctx, void *p)
 {
-	struct host_ws *ws = lz4e_ctx_attach(ctx, LZ4E_ATTACH_HOST_WS, sizeof(*ws), ws_dtor);
+	struct host_pool *hp = p;
+	int k;
+
+	for (k = 0; k < NWS; k++)
+		ws_release(ctx, &hp->ws[k]);
+}
+
+static int ws_init(lz4e_b200_ctx *ctx, struct host_ws *ws)
+{
 	int l, ok = 1;
 
-	if (!ws)
-		return NULL;
 	pthread_mutex_lock(&g_init_mu);
 	if (!ws->ready) {
 		for (l = 0; l < NLANES; l++) {
@@ -291,7 +302,31 @@ static struct host_ws *ws_get(lz4e_b200_ctx *ctx)
 		}
 	}
 	pthread_mutex_unlock(&g_init_mu);
-	return ws->ready ? ws : NULL;
+	return ws->ready;
+}
+
+/*
+ * A workspace of the context, LOCKED: the first one that is free, so that two
+ * threads (a compress batch and a decompress batch, say: one uploads, the other
+ * downloads, and PCIe is full duplex) run side by side on one GPU; a third
+ * caller waits for the first workspace.  Created on first use; NULL when that
+ * fails.
+ */
+static struct host_ws *ws_acquire(lz4e_b200_ctx *ctx)
+{
+	struct host_pool *hp = lz4e_ctx_attach(ctx, LZ4E_ATTACH_HOST_WS, sizeof(*hp), ws_dtor);
+	int k;
+
+	if (!hp)
+		return NULL;
+	for (k = 0; k < NWS; k++) {
+		if (!hp->ws[k].ready && !ws_init(ctx, &hp->ws[k]))
+			return NULL;
+		if (pthread_mutex_trylock(&hp->ws[k].mu) == 0)
+			return &hp->ws[k];
+	}
+	pthread_mutex_lock(&hp->ws[0].mu);
+	return &hp->ws[0];
 }
 
 /* the lane is idle when this is called */
@@ -918,14 +953,12 @@ static int run_batch(lz4e_b200_ctx *ctx, struct lz4e_b200_req *reqs, size_t n,
 		return LZ4E_B200_OK;
 	if (n > 0x7fffffffu)
 		return LZ4E_B200_EINVAL;
-	ws = ws_get(ctx);
+	ws = ws_acquire(ctx);
 	if (!ws) {
 		for (i = 0; i < n; i++)
 			reqs[i].ret = decompress ? -1 : 0;
 		return LZ4E_B200_EIO;
 	}
-
-	pthread_mutex_lock(&ws->mu);
 	t_start = now_ms();
 	memset(&ws->trace, 0, sizeof(ws->trace));
 	{

@@ -287,6 +287,7 @@ int simt_decompress_batch(const lz4e_b200_dev_bvec *src_bvecs,
 	a.in_scratch = nullptr;
 	a.in_stride = 0;
 	a.order = nullptr;
+	a.wave_serial = 14;
 	uint8_t *sm = (uint8_t *)smraw;
 
 	if (group == 1) {

@@ -306,6 +306,13 @@ def test_contexts_in_threads_and_destroy(ref_lib):
     for t in ts:
         t.join()
     assert not errs, errs
+    # two threads on ONE context: the context hands each batch its own workspace
+    ts = [threading.Thread(target=work, args=(c1, 3)) for _ in range(3)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
     c0.close()  # its arenas and workspace go with it
     work(c1, 1)
     c2 = pkg.Context(0)

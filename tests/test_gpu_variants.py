@@ -16,7 +16,7 @@ pytestmark = pytest.mark.gpu
 # 2 = pipelined group decoder, 1 = group decoder, 0/8 = round-1 group decoder
 DECODERS = [(0, 1), (3, 32), (2, 8), (2, 16), (1, 8), (0, 8)]
 DEFAULTS = {"dvariant": -1, "dgroup": 0, "dstage": -1, "dorder": 2048, "gin_small": 2,
-            "gin_min": 12288, "tma": 0}
+            "gin_min": 12288, "tma": 0, "wave_serial": 32}
 
 
 @pytest.fixture
