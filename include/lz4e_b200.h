@@ -211,6 +211,16 @@ int lz4e_b200_xfer_dev(lz4e_b200_ctx *ctx, void *stream,
 		       const struct lz4e_b200_dev_bvec *bvecs,
 		       const struct lz4e_b200_dev_iter *iters, const int32_t *lens,
 		       uint32_t nblocks, int to_host);
+/* the same, leaving out the first `skip` bytes of every block (they travelled
+ * another way, e.g. as the rows of a 2-D copy-engine transfer) */
+int lz4e_b200_xfer_skip_dev(lz4e_b200_ctx *ctx, void *stream,
+			    const struct lz4e_b200_dev_bvec *bvecs,
+			    const struct lz4e_b200_dev_iter *iters, const int32_t *lens,
+			    uint32_t nblocks, int to_host, uint32_t skip);
+/* `height` rows of `width` bytes, rows `spitch` / `dpitch` bytes apart, pinned
+ * host memory -> device, by copy engine */
+int lz4e_b200_copy2d_h2d(lz4e_b200_ctx *ctx, void *stream, void *dst_dev, size_t dpitch,
+			 const void *src_host, size_t spitch, size_t width, size_t height);
 /* bytes moved host -> device and device -> host through this context so far
  * (copy-engine copies enqueued + transfer-kernel bytes completed); waits for
  * nothing but reads a device counter, so call it after lz4e_b200_sync() */

@@ -80,6 +80,8 @@ def lib():
         "lz4e_b200_copy_h2d": (i32, [vp, vp, vp, vp, sz]),
         "lz4e_b200_copy_d2h": (i32, [vp, vp, vp, vp, sz]),
         "lz4e_b200_xfer_dev": (i32, [vp, vp, vp, vp, vp, u32, i32]),
+        "lz4e_b200_xfer_skip_dev": (i32, [vp, vp, vp, vp, vp, u32, i32, u32]),
+        "lz4e_b200_copy2d_h2d": (i32, [vp, vp, vp, sz, vp, sz, sz, sz]),
         "lz4e_b200_traffic": (i32, [vp, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
         "lz4e_b200_arena_create": (i32, [vp, sz, ctypes.POINTER(vp)]),
         "lz4e_b200_arena_destroy": (None, [vp]),

@@ -909,10 +909,28 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 	return LZ4E_B200_OK;
 }
 
+int lz4e_b200_copy2d_h2d(lz4e_b200_ctx *ctx, void *stream, void *dst_dev, size_t dpitch,
+			 const void *src_host, size_t spitch, size_t width, size_t height)
+{
+	cudaSetDevice(ctx->device);
+	CU(ctx, cudaMemcpy2DAsync(dst_dev, dpitch, src_host, spitch, width, height,
+				  cudaMemcpyHostToDevice, pick(ctx, stream)));
+	ctx->h2d_bytes += width * height;
+	return LZ4E_B200_OK;
+}
+
 int lz4e_b200_xfer_dev(lz4e_b200_ctx *ctx, void *stream,
 		       const struct lz4e_b200_dev_bvec *bvecs,
 		       const struct lz4e_b200_dev_iter *iters, const int32_t *lens,
 		       uint32_t nblocks, int to_host)
+{
+	return lz4e_b200_xfer_skip_dev(ctx, stream, bvecs, iters, lens, nblocks, to_host, 0);
+}
+
+int lz4e_b200_xfer_skip_dev(lz4e_b200_ctx *ctx, void *stream,
+			    const struct lz4e_b200_dev_bvec *bvecs,
+			    const struct lz4e_b200_dev_iter *iters, const int32_t *lens,
+			    uint32_t nblocks, int to_host, uint32_t skip)
 {
 	lz4e_xfer_args a;
 
@@ -926,6 +944,7 @@ int lz4e_b200_xfer_dev(lz4e_b200_ctx *ctx, void *stream,
 	a.lens = lens;
 	a.moved = ctx->d_moved + (to_host ? 1 : 0);
 	a.nblocks = nblocks;
+	a.skip = skip;
 	a.to_host = to_host ? 1 : 0;
 	a.narenas = 0;
 	{

@@ -47,6 +47,7 @@ struct lz4e_xfer_args {
 	const int32_t *lens; /* bytes per block (<= 0: none); NULL: bi_size */
 	unsigned long long *moved; /* byte counter, may be NULL */
 	uint32_t nblocks;
+	uint32_t skip; /* leave out the first `skip` bytes of every block */
 	int to_host;
 	int narenas;
 	struct {

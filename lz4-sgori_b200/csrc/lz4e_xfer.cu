@@ -42,6 +42,23 @@ __global__ void __launch_bounds__(256) lz4e_xfer_kernel(const lz4e_xfer_args a)
 		uint32_t done = it.bi_bvec_done;
 		int last = 0;
 
+		if (a.skip) { /* the head of the block travelled another way */
+			uint32_t sk = a.skip < len ? a.skip : len;
+
+			len -= sk;
+			while (sk) {
+				const uint32_t room = v->len - done;
+
+				if (sk < room) {
+					done += sk;
+					break;
+				}
+				sk -= room;
+				done = 0;
+				v++;
+			}
+		}
+
 		while (len) {
 			const uint32_t vlen = v->len;
 			uint32_t take = vlen - done;

@@ -62,6 +62,10 @@ struct side {
 	int stage_all;	/* pack every segment (arena pages too) into the staging buffer */
 	int all_linear; /* every block is a single segment */
 	int any_u16;	/* some block would select byU16 (compress source) */
+	/* regular layout: every block is ONE segment inside the same arena and the
+	 * blocks' first bytes are reg_pitch bytes apart (an array of slots) */
+	int reg_ok, reg_arena;
+	size_t reg_first, reg_prev, reg_pitch;
 };
 
 /*
@@ -122,7 +126,7 @@ struct host_ws {
 	/* LZ4E_B200_TRACE=1: where a batch spends its host time (stderr) */
 	struct {
 		double build, enqueue, wait, pack;
-		size_t bulk_up, bulk_down, kern_up, kern_down, packed_up; /* chunks per mode */
+		size_t bulk_up, bulk_down, kern_up, kern_down, packed_up, rows_up; /* chunks per mode */
 	} trace;
 };
 
@@ -493,6 +497,7 @@ static int side_add(struct arena_set *as, struct side *s, uint32_t blk,
 		s->bv[s->nbv].len = 0;
 		s->bv[s->nbv].rsvd = 0;
 		s->nbv++;
+		s->reg_ok = 0;
 		return LZ4E_B200_OK;
 	}
 	while (left) {
@@ -515,7 +520,20 @@ static int side_add(struct arena_set *as, struct side *s, uint32_t blk,
 			o->rsvd = 0;
 			range_add(&s->ar[k], off, off + take);
 			s->sum[k] += take;
+			if (s->reg_ok && nseg == 0) {
+				if (blk == 0) {
+					s->reg_arena = k;
+					s->reg_first = off;
+				} else if (k != s->reg_arena || off <= s->reg_prev ||
+					   (blk > 1 && off - s->reg_prev != s->reg_pitch)) {
+					s->reg_ok = 0;
+				} else if (blk == 1) {
+					s->reg_pitch = off - s->reg_prev;
+				}
+				s->reg_prev = off;
+			}
 		} else {
+			s->reg_ok = 0;
 			/* bounce: keep the host address's alignment mod 16 */
 			size_t off = (s->bounce_bytes + 15) & ~(size_t)15;
 			struct bounce *b;
@@ -547,8 +565,10 @@ static int side_add(struct arena_set *as, struct side *s, uint32_t blk,
 		idx++;
 		nseg++;
 	}
-	if (nseg > 1)
+	if (nseg > 1) {
 		s->all_linear = 0;
+		s->reg_ok = 0;
+	}
 	if (u16)
 		s->any_u16 = 1;
 	return LZ4E_B200_OK;
@@ -563,6 +583,8 @@ static void side_reset(struct side *s)
 	s->bn = bn;
 	s->cap_bn = cap;
 	s->all_linear = 1;
+	s->reg_ok = 1;
+	s->reg_arena = -1;
 }
 
 static void side_rebase_bounce(struct side *s, uint8_t *bounce_base)
@@ -681,6 +703,51 @@ static int sparse_src_mode(const struct side *s)
 	return span && sum * 4 >= span ? SPARSE_HULL : SPARSE_KERNEL;
 }
 
+/*
+ * Regular sparse sources (compressed blocks of very different sizes in equal
+ * slots): the first W bytes of every slot go up as the rows of ONE 2-D
+ * copy-engine transfer, what a block has beyond W through the transfer kernel.
+ * W minimises rows + 2 x excess (SM reads over PCIe cost about twice a copy-
+ * engine byte).  Returns W (a multiple of 64), or 0 when the spanned range is
+ * not worth cutting.
+ */
+static uint32_t pick_row_width(const struct side *s, size_t n, uint64_t *excess_out)
+{
+	uint64_t hist[65], best = 0, above_cnt = 0, above_sum = 0, sum = 0;
+	uint32_t bw = 64, best_w = 0;
+	size_t i;
+	int j;
+
+	if (!s->reg_ok || n < 64 || !s->reg_pitch || s->max_size > s->reg_pitch)
+		return 0;
+	while ((uint64_t)bw * 64 < s->max_size)
+		bw *= 2;
+	memset(hist, 0, sizeof(hist));
+	for (i = 0; i < n; i++) {
+		hist[(s->it[i].bi_size + bw - 1) / bw]++; /* sizes rounded up to a bucket edge */
+		sum += s->it[i].bi_size;
+	}
+	/* walk W down from the top bucket edge; `above` = blocks longer than W */
+	for (j = 64; j >= 1; j--) {
+		const uint64_t w = (uint64_t)j * bw;
+		/* excess over w of the blocks in buckets above j (upper bound) */
+		const uint64_t cost = n * w + 2 * (above_sum - above_cnt * w);
+
+		if (w <= s->reg_pitch && (!best_w || cost < best)) {
+			best = cost;
+			best_w = (uint32_t)w;
+			*excess_out = above_sum - above_cnt * w;
+		}
+		above_cnt += hist[j];
+		above_sum += hist[j] * (uint64_t)j * bw;
+	}
+	/* against the whole range by copy engine (n x pitch) */
+	if (!best_w || best * 10 > (uint64_t)n * s->reg_pitch * 8)
+		return 0;
+	(void)sum;
+	return best_w;
+}
+
 /* wait for a chunk and hand its results back to the caller's requests */
 static int lane_finish(lz4e_b200_ctx *ctx, struct host_ws *ws, struct lane *ln,
 		       int decompress, unsigned flags)
@@ -750,6 +817,8 @@ static int lane_submit(lz4e_b200_ctx *ctx, struct host_ws *ws, struct arena_set 
 {
 	size_t i, off, pin_bytes, o_sbv, o_dbv, o_sit, o_dit, sb;
 	int rc = LZ4E_B200_OK, l, src_kernel, dst_kernel;
+	uint32_t row_w = 0;
+	uint64_t row_excess = 0;
 	const int mode = xfer_mode();
 	double t0 = now_ms(), t1;
 	struct lz4e_b200_dev_bvec *d_sbv, *d_dbv;
@@ -802,6 +871,17 @@ static int lane_submit(lz4e_b200_ctx *ctx, struct host_ws *ws, struct arena_set 
 				    (flags & LZ4E_B200_F_DST_PRESERVE)));
 	if (!side_in_arenas(&ln->src))
 		src_kernel = 0;
+	/* sparse sources in equal slots as rows + excess: LZ4E_B200_SPARSE_SRC=rows.
+	 * Measured (profiles/r2k_e2e_timeline.md): 1.70 instead of 2.21 GB go up
+	 * per GiB step, but rows of under 2 KiB keep the copy engine below its
+	 * rate and the decompress batch takes 31.1 instead of 29.5 ms: not the
+	 * default */
+	{
+		const char *e = getenv("LZ4E_B200_SPARSE_SRC");
+
+		if (mode == 1 && !side_dense(&ln->src) && e && !strcmp(e, "rows"))
+			row_w = pick_row_width(&ln->src, n, &row_excess);
+	}
 	if (!side_in_arenas(&ln->dst))
 		dst_kernel = 0;
 	t1 = now_ms();
@@ -859,7 +939,17 @@ static int lane_submit(lz4e_b200_ctx *ctx, struct host_ws *ws, struct arena_set 
 	/* tables first: the transfer kernel reads them */
 	if (!rc)
 		rc = lz4e_b200_copy_h2d(ctx, ln->stream, ln->dev, ln->pin, ln->o_ret);
-	if (!rc && !(flags & LZ4E_B200_F_SRC_RESIDENT) && side_in_arenas(&ln->src)) {
+	if (!rc && !(flags & LZ4E_B200_F_SRC_RESIDENT) && side_in_arenas(&ln->src) && row_w) {
+		const int k = ln->src.reg_arena;
+
+		rc = lz4e_b200_copy2d_h2d(ctx, ln->stream, as->v[k].dev + ln->src.reg_first,
+					  ln->src.reg_pitch, as->v[k].host + ln->src.reg_first,
+					  ln->src.reg_pitch, row_w, n);
+		if (!rc && ln->src.max_size > row_w)
+			rc = lz4e_b200_xfer_skip_dev(ctx, ln->stream, d_sbv, d_sit, NULL, (uint32_t)n, 0,
+						     row_w);
+		ws->trace.rows_up++;
+	} else if (!rc && !(flags & LZ4E_B200_F_SRC_RESIDENT) && side_in_arenas(&ln->src)) {
 		if (src_kernel) {
 			rc = lz4e_b200_xfer_dev(ctx, ln->stream, d_sbv, d_sit, NULL, (uint32_t)n, 0);
 			ws->trace.kern_up++;
@@ -1064,12 +1154,13 @@ static int run_batch(lz4e_b200_ctx *ctx, struct lz4e_b200_req *reqs, size_t n,
 		fprintf(stderr,
 			"lz4e_b200: dev %d %s batch of %zu in %zu chunks: %.2f ms (table build %.2f, "
 			"packing %.2f, enqueue %.2f, waiting %.2f); source up: %zu chunks "
-			"by copy engine, %zu packed + copy engine, %zu by kernel; results down: %zu "
+			"by copy engine, %zu as rows + excess, %zu packed + copy engine, %zu by kernel; results down: %zu "
 			"by copy engine, %zu by kernel\n",
 			lz4e_b200_ctx_device(ctx), decompress ? "decompress" : "compress", n, nchunk,
 			now_ms() - t_start, ws->trace.build, ws->trace.pack,
 			ws->trace.enqueue - ws->trace.pack,
-			ws->trace.wait, ws->trace.bulk_up, ws->trace.packed_up, ws->trace.kern_up,
+			ws->trace.wait, ws->trace.bulk_up, ws->trace.rows_up, ws->trace.packed_up,
+			ws->trace.kern_up,
 			ws->trace.bulk_down, ws->trace.kern_down);
 	if (rc) {
 		fprintf(stderr, "lz4e_b200: batch failed (%d): %s\n", rc,

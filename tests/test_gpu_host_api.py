@@ -235,7 +235,7 @@ def test_batch_moves_exact_bytes(ctx, ref_lib, mode, monkeypatch):
     assert np.array_equal(out.arena.mem[:n * 4096], src.arena.mem[:n * 4096])
 
 
-@pytest.mark.parametrize("sparse", ["kernel", "hull", "pack"])
+@pytest.mark.parametrize("sparse", ["kernel", "hull", "pack", "rows"])
 def test_batch_sparse_source_modes(ctx, ref_lib, sparse, monkeypatch):
     """The three ways a sparse source side can go up give the same results."""
     monkeypatch.setenv("LZ4E_B200_SPARSE_SRC", sparse)
