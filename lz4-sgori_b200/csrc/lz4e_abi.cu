@@ -64,6 +64,7 @@ struct lz4e_b200_ctx {
 	int dorder;   /* cost-ordered work queue from this many blocks on; 0 = never */
 	int wave_min; /* blocks above 8 KiB: wave decoder from this many blocks on */
 	int wave_serial; /* wave decoder: sequence-serial copy from this many bytes per sequence */
+	int p12;      /* compress: packed 12-bit table for blocks <= 4 KiB */
 	int tma;      /* compress: TMA bulk staging of the input (shared-memory kernels) */
 	/* bytes moved between host and device through this context: copy engine
 	 * (host counters) and lz4e_xfer_kernel (device counters d_moved[0..1]) */
@@ -163,6 +164,9 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 	ctx->wave_serial = 32;
 	if (const char *e = getenv("LZ4E_B200_WAVE_SERIAL"))
 		ctx->wave_serial = atoi(e);
+	ctx->p12 = 0;
+	if (const char *e = getenv("LZ4E_B200_P12"))
+		ctx->p12 = atoi(e) ? 1 : 0;
 	ctx->tma = 0;
 	if (const char *e = getenv("LZ4E_B200_TMA"))
 		ctx->tma = atoi(e) ? 1 : 0;
@@ -261,6 +265,8 @@ int lz4e_b200_ctx_tune(lz4e_b200_ctx *ctx, const char *key, int value)
 		ctx->wave_min = value;
 	else if (!strcmp(key, "wave_serial"))
 		ctx->wave_serial = value;
+	else if (!strcmp(key, "p12"))
+		ctx->p12 = value ? 1 : 0;
 	else if (!strcmp(key, "tma"))
 		ctx->tma = value ? 1 : 0;
 	else if (!strcmp(key, "gin_min"))
@@ -622,6 +628,13 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 	a.nblocks = nblocks;
 	a.tma = (uint32_t)ctx->tma;
 	a.table_bytes = (flags & LZ4E_B200_DEV_NO_BYU16) ? 8192u : 16384u;
+	/* blocks of at most 4 KiB: 12-bit positions, 8192 entries in 12 KiB
+	 * (lz4e_table<.., P12>): 14 instead of 11 resident warps per SM.  An
+	 * option (LZ4E_B200_P12=1): sparse pages gain 13 %, but text loses 16 %
+	 * to the longer table update on its serial chain and the mixed batch
+	 * ends at 93.5 instead of 101.6 GB/s (profiles/r2ai_packed_table.md) */
+	if (!(flags & LZ4E_B200_DEV_NO_BYU16) && max_in_bytes <= 4096u && ctx->p12)
+		a.table_bytes = LZ4E_K_P12_BYTES;
 	if (max_in_bytes > 65536u) /* 32-bit positions: 4096 entries of 4 bytes */
 		a.table_bytes = 16384u;
 	a.in_cap = (max_in_bytes + 15u) & ~15u;

@@ -178,13 +178,66 @@ LZ4E_DEV void lz4e_put_run(uint8_t *p, uint32_t count, uint32_t last,
 }
 
 /*
+ * The hash table in shared memory.  Plain form: one TABT per entry.  Packed
+ * form (P12, blocks of at most 4 KiB in byU16 mode): positions fit 12 bits, so
+ * the 8192 entries take 12 KiB instead of 16 — low bytes in [0, 8192), high
+ * nibbles two to a byte in [8192, 12288) — and 14 instead of 11 warps are
+ * resident per SM.  Entry count, hash and "0 = empty = position 0" are the
+ * reference's (lz4e_compress.c:48-57, :98-168), so the bytes produced cannot
+ * change.  Two lanes that write entries h and h ^ 1 share a nibble byte: the
+ * warp-wide commits go in two passes (even entries, then odd ones).
+ */
+#define LZ4E_K_P12_BYTES 12288u
+template <typename TABT, bool P12>
+struct lz4e_table {
+	uint8_t *sm;
+
+	LZ4E_MEMBER uint32_t get(uint32_t h) const
+	{
+		if (P12) {
+			const uint32_t lo = sm[h];
+			const uint32_t hi = sm[8192u + (h >> 1)];
+
+			return lo | (((hi >> ((h & 1u) * 4u)) & 15u) << 8);
+		}
+		return reinterpret_cast<const TABT *>(sm)[h];
+	}
+	/* one lane, or lanes that are known not to share a nibble byte */
+	LZ4E_MEMBER void put(uint32_t h, uint32_t v) const
+	{
+		if (P12) {
+			uint8_t *p = sm + 8192u + (h >> 1);
+			const uint32_t sh = (h & 1u) * 4u;
+
+			sm[h] = (uint8_t)v;
+			*p = (uint8_t)((*p & ~(15u << sh)) | ((v >> 8) << sh));
+		} else {
+			reinterpret_cast<TABT *>(sm)[h] = (TABT)v;
+		}
+	}
+	/* every lane with `on` writes its own entry (all h distinct) */
+	LZ4E_MEMBER void commit(bool on, uint32_t h, uint32_t v) const
+	{
+		if (P12) {
+			if (on && !(h & 1u))
+				put(h, v);
+			lz4e_syncwarp(LZ4E_FULL);
+			if (on && (h & 1u))
+				put(h, v);
+		} else if (on) {
+			put(h, v);
+		}
+	}
+};
+
+/*
  * The encoder proper for one gathered block: d[0..n) in shared memory, table
  * `tab` (not yet cleared), output staging `out_area`.  TT is the hash-table
  * address mode LZ4E_fillBvIterSize selected (lz4e_compress.c:184-211).
  * Returns the reference's return value; src_end/dst_end receive the iterator
  * end state.
  */
-template <int TT, bool DIRECT, bool GIN, typename TABT>
+template <int TT, bool DIRECT, bool GIN, typename TABT, bool P12 = false>
 LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				      const struct lz4e_b200_dev_iter &di,
 				      const uint8_t *d, uint32_t n, uint8_t *sm,
@@ -192,7 +245,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				      uint32_t &src_end, uint32_t &dst_end)
 {
 	const uint32_t cap = di.bi_size;
-	TABT *tab = reinterpret_cast<TABT *>(sm);
+	const lz4e_table<TABT, P12> tab = { sm };
 	int32_t ret = 0;
 	/* 16-bit positions: the block is at most 64 KiB, so every candidate is
 	 * within LZ4E_DISTANCE_MAX (lz4e_compress.c:326-327 can never fire) */
@@ -245,9 +298,10 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 			/* the table — (1 << hashLog) entries of TABT, 16-bit positions
 			 * up to 64 KiB, 32-bit ones above — was zeroed by the caller
 			 * while the block's bytes were still in flight */
-			const uint32_t tbytes = (TT == LZ4E_TT_U16   ? 8192u
-						 : TT == LZ4E_TT_U32 ? 4096u
-								     : 2048u) * (uint32_t)sizeof(TABT);
+			const uint32_t tbytes = P12 ? LZ4E_K_P12_BYTES
+						    : (TT == LZ4E_TT_U16   ? 8192u
+						       : TT == LZ4E_TT_U32 ? 4096u
+									   : 2048u) * (uint32_t)sizeof(TABT);
 
 			if (tbytes > a.table_bytes) {
 				/* launched for byU32-only batches, block wants byU16 */
@@ -288,7 +342,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 
 					seq = lz4e_sld_seq5(da, pos + dm, b4);
 					h = lz4e_hash(seq, b4, TT);
-					m = tab[h];
+					m = tab.get(h);
 				}
 				const uint32_t peers = lz4e_match_any(LZ4E_FULL, h);
 				const uint32_t lower = peers & ((1u << lane) - 1u);
@@ -316,8 +370,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 						break;
 					}
 					/* commit all 32 visits, keep searching */
-					if ((peers >> lane) >> 1 == 0)
-						tab[h] = (TABT)pos;
+					tab.commit((peers >> lane) >> 1 == 0, h, pos);
 					lz4e_syncwarp(LZ4E_FULL);
 					kbase += 32;
 					continue;
@@ -326,9 +379,9 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				/* ---- a match: commit visits 0..f in serial order ---- */
 				const int f = lz4e_ffs(okmask) - 1;
 
-				if ((int)lane <= f &&
-				    (peers & ((2u << f) - 1u) & ~((2u << lane) - 1u)) == 0)
-					tab[h] = (TABT)pos;
+				tab.commit((int)lane <= f &&
+						   (peers & ((2u << f) - 1u) & ~((2u << lane) - 1u)) == 0,
+					   h, pos);
 
 				ip = lz4e_shfl(LZ4E_FULL, pos, f);
 				mp = lz4e_shfl(LZ4E_FULL, m, f);
@@ -364,7 +417,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					const uint32_t sq = lz4e_funnel_r(lo, hi, 16u); /* bytes q..   */
 					const uint32_t qh = lz4e_hash(sq, (hi >> 16) & 0xffu, TT);
 					const uint32_t qh2 = lz4e_hash(lo, hi & 0xffu, TT);
-					const uint32_t qm = qh2 == qh ? q - 2u : (uint32_t)tab[qh];
+					const uint32_t qm = qh2 == qh ? q - 2u : tab.get(qh);
 					const bool fne = lane >= matchlimit - fip ||
 							 (sq & 0xffu) != d[mp + 4u + lane];
 					const bool qok = (NEAR || qm + 65535u >= q) && lz4e_sld32u(da, qm + dm) == sq;
@@ -395,8 +448,8 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					/* the lane that guessed the length holds the hashes of
 					 * :461-464 and :467-470 for the new anchor q == na */
 					if (lane == ml && !last) {
-						tab[qh2] = (TABT)(q - 2u);
-						tab[qh] = (TABT)q;
+						tab.put(qh2, q - 2u);
+						tab.put(qh, q);
 					}
 					anchor = ip = na;
 					p0 = na + 1u; /* if no match follows: search from ip + 1 */
@@ -449,7 +502,7 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 
 						q_h = lz4e_hash(sq, b4q, TT);
 						q_h2 = lz4e_hash(sp, b4p, TT);
-						q_m = q_h2 == q_h ? q - 2u : (uint32_t)tab[q_h];
+						q_m = q_h2 == q_h ? q - 2u : tab.get(q_h);
 						q_ok = (NEAR || q_m + 65535u >= q) && lz4e_sld32u(da, q_m + dm) == sq;
 					}
 					if (lim) { /* uniform: 0 after an immediate match */
@@ -596,8 +649,8 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 
 					mp = lz4e_shfl(LZ4E_FULL, q_m, (int)ml);
 					if (lane == ml) {
-						tab[q_h2] = (TABT)(anchor - 2u);
-						tab[q_h] = (TABT)anchor;
+						tab.put(q_h2, anchor - 2u);
+						tab.put(q_h, anchor);
 					}
 					ip = anchor;
 					have = (okm >> ml) & 1u; /* else: search from ip + 1 */
@@ -664,6 +717,7 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 	int tt = LZ4E_TT_U16;
 	int32_t ret = 0;
 	uint32_t src_end = 0, dst_end = 0;
+	bool p12 = false;
 
 	if (n > LZ4E_K_MAX_INPUT) /* lz4e_compress.c:245-248 */
 		goto done;
@@ -756,11 +810,14 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 		if (TMA && bulk && lane == 0)
 			lz4e_mbar_arrive(bar);
 #endif
+		/* packed table: the launch reserved 12 KiB, this block is byU16 */
+		p12 = !GIN && tt == LZ4E_TT_U16 && a.table_bytes == LZ4E_K_P12_BYTES && n <= 4096u;
 		if (!(too_many && n >= 13) && n >= 13) {
 			/* zero the table while the bulk copies land */
 			const uint32_t tbytes =
-				(tt == LZ4E_TT_U16 ? 8192u : tt == LZ4E_TT_U32 ? 4096u : 2048u) *
-				(n > 65536u ? 4u : 2u);
+				p12 ? LZ4E_K_P12_BYTES
+				    : (tt == LZ4E_TT_U16 ? 8192u : tt == LZ4E_TT_U32 ? 4096u : 2048u) *
+					      (n > 65536u ? 4u : 2u);
 			const lz4e_u128 z = { 0, 0, 0, 0 };
 
 			if (tbytes <= a.table_bytes)
@@ -795,8 +852,12 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 	}
 	switch (tt) {
 	case LZ4E_TT_U16:
-		ret = lz4e_compress_encode<LZ4E_TT_U16, DIRECT, GIN, uint16_t>(
-			a, di, d, n, sm, out_area, lane, src_end, dst_end);
+		if (!GIN && p12)
+			ret = lz4e_compress_encode<LZ4E_TT_U16, DIRECT, GIN, uint16_t, true>(
+				a, di, d, n, sm, out_area, lane, src_end, dst_end);
+		else
+			ret = lz4e_compress_encode<LZ4E_TT_U16, DIRECT, GIN, uint16_t>(
+				a, di, d, n, sm, out_area, lane, src_end, dst_end);
 		break;
 	case LZ4E_TT_U32:
 		ret = lz4e_compress_encode<LZ4E_TT_U32, DIRECT, GIN, uint16_t>(

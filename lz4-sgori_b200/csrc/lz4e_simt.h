@@ -18,6 +18,7 @@
 #if defined(__CUDACC__)
 
 #define LZ4E_DEV __device__ __forceinline__
+#define LZ4E_MEMBER __device__ __forceinline__ /* member functions */
 /* rare paths are kept out of line so that the hot loops stay small enough for
  * the instruction cache */
 #define LZ4E_DEV_NOINLINE __device__ __noinline__

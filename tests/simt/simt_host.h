@@ -17,6 +17,7 @@
 #include <stdint.h>
 
 #define LZ4E_DEV static inline __attribute__((always_inline))
+#define LZ4E_MEMBER inline
 #define LZ4E_DEV_NOINLINE static __attribute__((noinline))
 #define LZ4E_FULL 0xffffffffu
 #define LZ4E_ASSUME_GLOBAL(p) ((void)(p))

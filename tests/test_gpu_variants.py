@@ -16,7 +16,7 @@ pytestmark = pytest.mark.gpu
 # 2 = pipelined group decoder, 1 = group decoder, 0/8 = round-1 group decoder
 DECODERS = [(0, 1), (3, 32), (2, 8), (2, 16), (1, 8), (0, 8)]
 DEFAULTS = {"dvariant": -1, "dgroup": 0, "dstage": -1, "dorder": 2048, "gin_small": 2,
-            "gin_min": 12288, "tma": 0, "wave_serial": 32}
+            "gin_min": 12288, "tma": 0, "wave_serial": 32, "p12": 0}
 
 
 @pytest.fixture
@@ -121,3 +121,20 @@ def test_tma_staged_input_parity(ctx, ref_lib, tuned):
     P.test_fuzz_segmentations_and_sizes(ctx, ref_lib)
     P.test_limited_output(ctx, ref_lib)
     P.test_survey_sanity_values(ctx, ref_lib)
+
+
+@pytest.mark.parametrize("p12", [0, 1])
+def test_packed_table_parity(ctx, ref_lib, tuned, p12):
+    """Blocks of at most 4 KiB: the packed 12-bit hash table (an option) and the plain 16-bit one
+    produce the reference's bytes; larger blocks in other launches are unaffected."""
+    tuned(p12=p12)
+    P.test_config2_4k_mixed(ctx, ref_lib)
+    P.test_limited_output(ctx, ref_lib)
+    rng = np.random.default_rng(77)
+    datas, specs = [], []
+    for i in range(200):
+        n = int(rng.choice([0, 1, 12, 13, 14, 100, 4095, 4096])) if rng.random() < 0.4 \
+            else int(rng.integers(0, 4097))
+        datas.append(common.synth(n, int(rng.integers(0, 4)), i))
+        specs.append(sg.segs_random(n, rng, max_segs=10))
+    P._check_compress(ctx, ref_lib, datas, specs)

@@ -77,6 +77,37 @@ def test_compress_body_limited_output(simt, ref_lib, out_cap):
         assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
 
 
+@pytest.mark.parametrize("out_cap", [1024, 4352, 64])
+def test_compress_body_packed_table(simt, ref_lib, out_cap):
+    """Blocks of at most 4 KiB with the packed 12-bit table (12 KiB for the 8192 byU16 entries):
+    same bytes as the reference on every class, on sizes around the limits, on page-split and
+    odd segmentations (byU16) and on a multi-page bvec (byU32 inside the same launch)."""
+    rng = np.random.default_rng(12)
+    datas, specs = [], []
+    for c in range(4):
+        for n in (4096, 4095, 2500, 300, 13, 12, 0):
+            datas.append(common.synth(n, c, 31 * c + n))
+            specs.append(sg.segs_single(n))
+    for b in range(8):  # several small segments: still byU16
+        n = int(rng.integers(500, 4097))
+        datas.append(common.synth(n, b & 3, 500 + b))
+        specs.append(sg.segs_random(n, rng, max_segs=8, allow_big=False))
+    datas.append(common.lcg_text(4096))  # raw bv_len above 4096: byU32, plain 8 KiB table
+    specs.append({"size": 4096, "segs": [(100, 6000)], "skip": 700})
+    datas.append(np.zeros(4096, np.uint8))
+    specs.append(sg.segs_single(4096))
+    src = _host_layout(specs, datas)
+    dspecs = [sg.segs_single(sg.compress_bound(len(d))) for d in datas]
+    dst = _host_layout(dspecs)
+    dst.arena.mem[:] = 0xEE
+    rets, ends, faults = emu.compress(simt, src, dst, in_cap=4096, out_cap=out_cap, table_bytes=12288)
+    ref_dst, (ref_rets, _) = common.oracle_compress(ref_lib, src, dspecs)
+    assert faults == 0
+    assert np.array_equal(rets, ref_rets)
+    for b in range(len(datas)):
+        assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
+
+
 @pytest.mark.parametrize("group", [1, 2, 4, 8, 16, 32])
 def test_decompress_body_roundtrip(simt, ref_lib, group):
     datas, specs = _cases()
