@@ -120,7 +120,7 @@ void lz4e_dev_stats_reset(struct lz4e_dev *dev);
 /* bytes the codec produced for the writes so far (compressed size) */
 uint64_t lz4e_dev_compressed_bytes(struct lz4e_dev *dev);
 /* order-independent digest of WHAT the codec produced: the wrapping sum, over
- * all successful writes so far, of lz4e_fnv1a64() of each bio's compressed
+ * all successful writes so far, of lz4e_fnv1a64() (a word-wise FNV-1a variant) of each bio's compressed
  * bytes — lets a harness compare the bytes of every bio with the reference's
  * without keeping them */
 uint64_t lz4e_dev_compressed_digest(struct lz4e_dev *dev);

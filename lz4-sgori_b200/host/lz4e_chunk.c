@@ -9,6 +9,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 #include "../../include/lz4e.h"
 #include "../../include/lz4e_chunk.h"
@@ -528,13 +529,23 @@ uint64_t lz4e_dev_compressed_digest(struct lz4e_dev *dev)
 	return dev->compressed_digest;
 }
 
+/* FNV-1a style digest over 64-bit little-endian words (tail bytes one by one):
+ * eight times fewer multiplies than the byte-wise form, which cost more than
+ * the codec in the request path */
 uint64_t lz4e_fnv1a64(const void *p, size_t n)
 {
 	const uint8_t *b = p;
-	uint64_t h = 1469598103934665603ull;
-	size_t i;
+	uint64_t h = 1469598103934665603ull ^ (uint64_t)n;
+	size_t i = 0;
 
-	for (i = 0; i < n; i++)
+	for (; i + 8 <= n; i += 8) {
+		uint64_t w;
+
+		memcpy(&w, b + i, 8);
+		h = (h ^ w) * 1099511628211ull;
+		h ^= h >> 29;
+	}
+	for (; i < n; i++)
 		h = (h ^ b[i]) * 1099511628211ull;
 	return h;
 }
@@ -545,6 +556,14 @@ static unsigned short bytes_to_pages(size_t bytes)
 	size_t pages = (bytes + PAGE_SIZE - 1) / PAGE_SIZE;
 
 	return (unsigned short)(pages < BIO_MAX_VECS ? pages : BIO_MAX_VECS);
+}
+
+static double chunk_now_ms(void)
+{
+	struct timespec ts;
+
+	clock_gettime(CLOCK_MONOTONIC, &ts);
+	return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
 }
 
 struct wreq {
@@ -560,6 +579,8 @@ int lz4e_dev_submit_writes(struct lz4e_dev *dev, struct bio **bios, size_t n, in
 	size_t *map = calloc(n ? n : 1, sizeof(*map));
 	int *st = calloc(n ? n : 1, sizeof(*st));
 	size_t i, k, nlive = 0;
+	const int trace = getenv("LZ4E_CHUNK_TRACE") != NULL;
+	double t0 = chunk_now_ms(), t1, t2, t3, t4;
 
 	if (!w || !live || !map || !st) {
 		for (i = 0; i < n; i++)
@@ -604,7 +625,9 @@ int lz4e_dev_submit_writes(struct lz4e_dev *dev, struct bio **bios, size_t n, in
 	}
 	/* compress every bio as one block, then decompress it again
 	 * (lz4e_req.c:177-189), each step ONE GPU batch */
+	t1 = chunk_now_ms();
 	lz4e_chunk_compress_ext_batch(live, nlive, st);
+	t2 = chunk_now_ms();
 	for (k = 0, i = 0; k < nlive; k++) {
 		if (st[k]) {
 			status[map[k]] = st[k];
@@ -616,6 +639,7 @@ int lz4e_dev_submit_writes(struct lz4e_dev *dev, struct bio **bios, size_t n, in
 	nlive = i;
 	/* the compressed bytes are still current in the device mirror */
 	chunk_batch(live, nlive, st, OP_DECOMPRESS, LZ4E_B200_F_SRC_RESIDENT);
+	t3 = chunk_now_ms();
 	pthread_mutex_lock(&dev->mu);
 	for (k = 0; k < nlive; k++) {
 		struct bio *ob = bios[map[k]];
@@ -637,6 +661,12 @@ int lz4e_dev_submit_writes(struct lz4e_dev *dev, struct bio **bios, size_t n, in
 		stats_update(&dev->write_stats, status[i] != 0,
 			     bytes_to_pages(bios[i]->bi_iter.bi_size), bios[i]->bi_iter.bi_size);
 	pthread_mutex_unlock(&dev->mu);
+	t4 = chunk_now_ms();
+	if (trace)
+		fprintf(stderr,
+			"lz4e_chunk: %zu writes: set-up %.2f ms, compress batch %.2f, verify "
+			"(decompress) batch %.2f, store + stats %.2f\n",
+			n, t1 - t0, t2 - t1, t3 - t2, t4 - t3);
 out:
 	for (i = 0; w && i < n; i++) {
 		lz4e_chunk_free(w[i].chunk);
