@@ -69,6 +69,18 @@ struct lz4e_lane_smem {
 	lz4e_u128 unit[LZ4E_L_TAB + LZ4E_L_PAD];
 };
 
+/* the 8 bytes at p (any alignment, little endian) from two aligned 8-byte
+ * loads; reads up to 15 bytes past p */
+LZ4E_DEV uint64_t lz4e_ld64u(const uint8_t *p)
+{
+	const uintptr_t a = (uintptr_t)p;
+	const uint64_t *q = (const uint64_t *)(a & ~(uintptr_t)7);
+	const uint32_t sh = (uint32_t)(a & 7u) * 8u;
+	const uint64_t lo = q[0], hi = q[1];
+
+	return sh ? (lo >> sh) | (hi << (64u - sh)) : lo;
+}
+
 /* inclusive prefix sum over the warp; *total = sum over all lanes */
 LZ4E_DEV uint32_t lz4e_lane_scan(uint32_t v, uint32_t lane, uint32_t *total)
 {
@@ -414,18 +426,29 @@ LZ4E_DEV void lz4e_decompress_lanes(const lz4e_decompress_args &a,
 			 * most one extension byte per length, far enough from both ends
 			 * that none of the reference's end-of-block rules can fire.
 			 */
-			if ((int32_t)ip + 4 <= iend) {
-				const uint32_t tok = inb[ip];
-				const uint32_t e1 = inb[ip + 1u];
+			if ((int32_t)ip + 16 <= iend) {
+				/*
+				 * The 8 bytes at ip in one register pair (two aligned 8-byte
+				 * loads): token, literal-length byte and — when the literal
+				 * run is at most 3-4 bytes, which is nearly always — offset
+				 * and match-length byte as well.  Every lane reads its own
+				 * stream, so a byte load is 32 sectors for 32 bytes: five of
+				 * them per sequence were half of this kernel's LSU traffic.
+				 */
+				const uint64_t w = lz4e_ld64u(inb + ip);
+				const uint32_t tok = (uint32_t)w & 0xffu;
+				const uint32_t e1 = ((uint32_t)w >> 8) & 0xffu;
 				const uint32_t lext = (tok >> 4) == 15u;
 				const uint32_t lit = (tok >> 4) + (lext ? e1 : 0u);
 				const uint32_t lp = ip + 1u + lext;
 				const uint32_t fp = lp + lit;
 
-				if (!(lext && e1 == 255u) && (int32_t)fp + 15 <= iend) {
-					const uint32_t off = (uint32_t)inb[fp] |
-							     ((uint32_t)inb[fp + 1u] << 8);
-					const uint32_t e2 = inb[fp + 2u];
+				if (!(lext && e1 == 255u) && (int32_t)fp + 16 <= iend) {
+					const uint32_t rel = fp - ip;
+					const uint64_t w2 = rel <= 5u ? w >> (8u * rel)
+								      : lz4e_ld64u(inb + fp);
+					const uint32_t off = (uint32_t)w2 & 0xffffu;
+					const uint32_t e2 = ((uint32_t)w2 >> 16) & 0xffu;
 					const uint32_t mext = (tok & 15u) == 15u;
 					const uint32_t mlen = (tok & 15u) + 4u + (mext ? e2 : 0u);
 
