@@ -548,9 +548,10 @@ def run_e2e(torch, pkg, ctx, args, dist=None, rank=0, world=1, local=0):
     # How compressed blocks (40 % of their LZ4E_COMPRESSBOUND slots) go up for decompression:
     # alone on the host a GPU is fastest with one copy-engine transfer of the spanned range
     # (29.5 vs 33 ms per GiB); when several GPUs share the host's memory system the bytes count
-    # and the exact-byte transfer kernel wins (8 GPUs: 45.1 vs 39.8 GB/s,
-    # profiles/r2ab_e2e_n8.md).  The library's default is the former; set per deployment.
-    if world > 1:
+    # and the exact-byte transfer kernel wins (8 GPUs: 45.1 vs 39.8 GB/s, 4 GPUs: 33.4 vs 30.8;
+    # 2 GPUs still prefer the range: 33.6 vs 29.1; profiles/r2ab_e2e_n8.md).  The library's
+    # default is the former; set per deployment.
+    if world >= 4:
         os.environ.setdefault("LZ4E_B200_SPARSE_SRC", "kernel")
     src_arena = pkg.Arena(ctx, nb + 1)
     dst_pages = (nb * DST_STRIDE + 4095) // 4096 + 2
