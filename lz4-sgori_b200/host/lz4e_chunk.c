@@ -566,6 +566,57 @@ static double chunk_now_ms(void)
 	return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
 }
 
+#define STORE_THREADS 4
+
+struct store_job {
+	struct lz4e_dev *dev;
+	struct bio **bios;
+	struct lz4e_chunk **live;
+	const size_t *map;
+	const int *st;
+	int *status;
+	size_t nlive, first, unused, stride;
+	uint64_t cbytes, digest;
+};
+
+/*
+ * Thread `first` of `stride`: the part of every chunk's decompressed bytes that
+ * falls into this thread's slice of the RAM device, chunks in submission order
+ * (writes of one batch may overlap: the later bio wins, as it does when they
+ * are applied one after the other); size and digest of the compressed bytes
+ * for every stride-th chunk.
+ */
+static void *store_main(void *p)
+{
+	struct store_job *j = p;
+	const uint64_t cap = j->dev->capacity;
+	const uint64_t lo = cap / j->stride * j->first;
+	const uint64_t hi = j->first + 1 == j->stride ? cap : cap / j->stride * (j->first + 1);
+	size_t k;
+
+	for (k = 0; k < j->nlive; k++) {
+		struct bio *ob = j->bios[j->map[k]];
+		struct lz4e_chunk *c = j->live[k];
+		const uint64_t pos = (uint64_t)ob->bi_iter.bi_sector * 512u;
+		const uint64_t end = pos + (uint64_t)c->src_buf.data_size;
+		const uint64_t a = pos > lo ? pos : lo, b = end < hi ? end : hi;
+
+		if (j->st[k]) {
+			if (j->first == 0)
+				j->status[j->map[k]] = j->st[k];
+			continue;
+		}
+		if (a < b)
+			memcpy(j->dev->store + a, (const char *)c->src_buf.data + (a - pos),
+			       (size_t)(b - a));
+		if (k % j->stride == j->first) {
+			j->cbytes += (uint64_t)c->dst_buf.data_size;
+			j->digest += lz4e_fnv1a64(c->dst_buf.data, (size_t)c->dst_buf.data_size);
+		}
+	}
+	return NULL;
+}
+
 struct wreq {
 	struct lz4e_chunk *chunk;
 	struct bio new_bio;
@@ -641,21 +692,44 @@ int lz4e_dev_submit_writes(struct lz4e_dev *dev, struct bio **bios, size_t n, in
 	chunk_batch(live, nlive, st, OP_DECOMPRESS, LZ4E_B200_F_SRC_RESIDENT);
 	t3 = chunk_now_ms();
 	pthread_mutex_lock(&dev->mu);
-	for (k = 0; k < nlive; k++) {
-		struct bio *ob = bios[map[k]];
-		struct lz4e_chunk *c = live[k];
-
-		if (st[k]) {
-			status[map[k]] = st[k];
-			continue;
-		}
+	{
 		/* the new bio is reset and loaded with the DECOMPRESSED buffer
-		 * (lz4e_req.c:191-199); the RAM device takes its bytes */
-		memcpy(dev->store + (uint64_t)ob->bi_iter.bi_sector * 512u, c->src_buf.data,
-		       (size_t)c->src_buf.data_size);
-		dev->compressed_bytes += (uint64_t)c->dst_buf.data_size;
-		dev->compressed_digest +=
-			lz4e_fnv1a64(c->dst_buf.data, (size_t)c->dst_buf.data_size);
+		 * (lz4e_req.c:191-199); the RAM device takes its bytes.  A handful of
+		 * threads for a large batch: the copy out of just-DMA-written pinned
+		 * pages is the one part of the request path that is pure host memory
+		 * traffic (2.5 ms of a 9 ms batch on one thread) */
+		struct store_job job = { dev, bios, live, map, st, status, nlive, 0, 0, 1, 0, 0 };
+		pthread_t th[STORE_THREADS - 1];
+		struct store_job jobs[STORE_THREADS];
+		size_t bytes = 0;
+		int nt = 1, t;
+
+		for (k = 0; k < nlive; k++)
+			bytes += (size_t)live[k]->src_buf.buf_size;
+		if (bytes >= ((size_t)2 << 20) && nlive >= 2 * STORE_THREADS)
+			nt = STORE_THREADS;
+		for (t = 0; t < nt; t++) {
+			jobs[t] = job;
+			jobs[t].first = (size_t)t;
+			jobs[t].stride = (size_t)nt;
+		}
+		for (t = 1; t < nt; t++)
+			if (pthread_create(&th[t - 1], NULL, store_main, &jobs[t])) {
+				jobs[t].stride = 0; /* not started: done below */
+			}
+		store_main(&jobs[0]);
+		for (t = 1; t < nt; t++) {
+			if (jobs[t].stride)
+				pthread_join(th[t - 1], NULL);
+			else {
+				jobs[t].stride = (size_t)nt;
+				store_main(&jobs[t]);
+			}
+		}
+		for (t = 0; t < nt; t++) {
+			dev->compressed_bytes += jobs[t].cbytes;
+			dev->compressed_digest += jobs[t].digest;
+		}
 	}
 	for (i = 0; i < n; i++)
 		stats_update(&dev->write_stats, status[i] != 0,
