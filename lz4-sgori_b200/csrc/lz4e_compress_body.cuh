@@ -405,22 +405,33 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 				bool ended = false;
 
 				if (fast_ok && have && ip == anchor) {
+				/*
+				 * The input words of a round are loaded one round EARLY: as
+				 * soon as the length of this match (-> next anchor) and its
+				 * successor's candidate are known, i.e. before this round's
+				 * validity vote, sequence bytes and table update.  The block
+				 * is read-only, so the early loads cannot see a stale value;
+				 * the reads may reach a few bytes into the slack behind the
+				 * block like the unguarded loads of the round itself.
+				 */
+				uint32_t w0, w1, w2, sh, mb;
+				{
+					const uint32_t tq = ip + 4u + lane - 2u + dm;
+					const uint8_t *al = da + (tq & ~3u);
+
+					sh = tq << 3;
+					w0 = lz4e_ld32a(al), w1 = lz4e_ld32a(al + 4), w2 = lz4e_ld32a(al + 8);
+					mb = d[mp + 4u + lane];
+				}
 				for (;;) {
 					const uint32_t fip = ip + 4u, q = fip + lane;
-					const uint32_t tq = q - 2u + dm;
-					const uint8_t *al = da + (tq & ~3u);
-					const uint32_t sh = tq << 3;
-					const uint32_t w0 = lz4e_ld32a(al), w1 = lz4e_ld32a(al + 4),
-						       w2 = lz4e_ld32a(al + 8);
 					const uint32_t lo = lz4e_funnel_r(w0, w1, sh); /* bytes q-2.. */
 					const uint32_t hi = lz4e_funnel_r(w1, w2, sh); /* bytes q+2.. */
 					const uint32_t sq = lz4e_funnel_r(lo, hi, 16u); /* bytes q..   */
 					const uint32_t qh = lz4e_hash(sq, (hi >> 16) & 0xffu, TT);
 					const uint32_t qh2 = lz4e_hash(lo, hi & 0xffu, TT);
 					const uint32_t qm = qh2 == qh ? q - 2u : tab.get(qh);
-					const bool fne = lane >= matchlimit - fip ||
-							 (sq & 0xffu) != d[mp + 4u + lane];
-					const bool qok = (NEAR || qm + 65535u >= q) && lz4e_sld32u(da, qm + dm) == sq;
+					const bool fne = lane >= matchlimit - fip || (sq & 0xffu) != mb;
 					const uint32_t fnz = lz4e_ballot(LZ4E_FULL, fne);
 
 					if (fnz == 0)
@@ -428,6 +439,19 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					const uint32_t ml = (uint32_t)lz4e_ffs(fnz) - 1u;
 					const uint32_t na = fip + ml;
 					const uint32_t off = ip - mp;
+					const uint32_t cand = lz4e_sld32u(da, qm + dm);
+
+					mp = lz4e_shfl(LZ4E_FULL, qm, (int)ml);
+					{ /* next round's loads, see above */
+						const uint32_t tq = na + 4u + lane - 2u + dm;
+						const uint8_t *al = da + (tq & ~3u);
+
+						sh = tq << 3;
+						w0 = lz4e_ld32a(al), w1 = lz4e_ld32a(al + 4),
+						w2 = lz4e_ld32a(al + 8);
+						mb = d[mp + 4u + lane];
+					}
+					const bool qok = (NEAR || qm + 65535u >= q) && cand == sq;
 
 					if (!whole && op - st.win + 4u > st.cap)
 						lz4e_stage_flush(st, op, a.out_cap, lane);
@@ -444,7 +468,6 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 					op += 3u + (ml >= 15u ? 1u : 0u);
 					const uint32_t okm = lz4e_ballot(LZ4E_FULL, qok);
 
-					mp = lz4e_shfl(LZ4E_FULL, qm, (int)ml);
 					/* the lane that guessed the length holds the hashes of
 					 * :461-464 and :467-470 for the new anchor q == na */
 					if (lane == ml && !last) {
