@@ -1,0 +1,6 @@
+for v in lb9 cur; do
+  if [ $v = cur ]; then unset LZ4E_B200_LIB; else export LZ4E_B200_LIB=$PWD/variants/lib_$v.so; fi
+  echo "== $v" >> gpurun_out/r2az.log
+  DBENCH_ONLY=0,1,-1,1 python tools/dbench.py 262144 0 5 2>&1 | grep variant >> gpurun_out/r2az.log
+  python tools/class_bench.py 131072 3 2>&1 | grep class | cut -c1-12,80-120 >> gpurun_out/r2az.log
+done
