@@ -58,6 +58,12 @@ struct lz4e_chunk {
  * before the first allocation.  pool_pages = 0 keeps the default pool size
  * ($LZ4E_CHUNK_POOL_MB, 1024 MiB). */
 int lz4e_chunk_setup(lz4e_b200_ctx *ctx, size_t pool_pages);
+/* Several GPUs from one process: every context has its own pool (created by
+ * lz4e_chunk_setup(ctx, ...) or on first use), and a thread chooses the context
+ * its chunk and request-path calls run on with lz4e_chunk_bind(ctx) (NULL:
+ * back to the default).  One submitter thread per GPU is the intended shape;
+ * a batch runs on the context whose pool holds its chunks. */
+void lz4e_chunk_bind(lz4e_b200_ctx *ctx);
 /* release the pool (all chunks must have been freed) */
 void lz4e_chunk_teardown(void);
 

@@ -24,8 +24,16 @@
  * back from the device in one bulk copy, which may overwrite free pages that
  * lie inside that range */
 
-static pthread_mutex_t p_mu = PTHREAD_MUTEX_INITIALIZER;
-static struct {
+/*
+ * One pool per CONTEXT (= per GPU), found through a small registry; a thread
+ * chooses the context its chunk calls run on with lz4e_chunk_bind(), so one
+ * process can drive several GPUs through the chunk layer (one submitter thread
+ * per GPU).  Threads that never bind use the context of the first
+ * lz4e_chunk_setup(), else the default context.
+ */
+#define MAX_POOLS 16
+
+struct pool {
 	lz4e_b200_ctx *ctx;
 	lz4e_b200_arena *arena;
 	uint8_t *base;
@@ -33,34 +41,70 @@ static struct {
 	size_t freel[POOL_CLASSES]; /* first free run of that many pages, + 1 */
 	size_t *next;		    /* per page index */
 	size_t live;
-	int ready;
-} pool;
+};
+
+static pthread_mutex_t p_mu = PTHREAD_MUTEX_INITIALIZER; /* registry and every pool */
+static struct pool *g_pools[MAX_POOLS];
+static lz4e_b200_ctx *g_first_ctx;	   /* context of the first lz4e_chunk_setup() */
+static __thread lz4e_b200_ctx *t_ctx;	   /* lz4e_chunk_bind() of this thread */
+
+static void pool_release_locked(int i)
+{
+	struct pool *pl = g_pools[i];
+
+	g_pools[i] = NULL;
+	if (g_first_ctx == pl->ctx)
+		g_first_ctx = NULL;
+	lz4e_b200_arena_destroy(pl->arena);
+	free(pl->next);
+	free(pl);
+}
 
 /* the pool's context is being destroyed: the pool goes with it (chunks still
  * alive keep dangling buffers — a caller bug, reported) */
 static void pool_ctx_dtor(lz4e_b200_ctx *ctx, void *p)
 {
+	int i;
+
 	(void)p;
 	pthread_mutex_lock(&p_mu);
-	if (pool.ready && pool.ctx == ctx) {
-		if (pool.live)
-			fprintf(stderr, "lz4e_chunk: context destroyed with %zu pool buffers live\n",
-				pool.live);
-		lz4e_b200_arena_destroy(pool.arena);
-		free(pool.next);
-		memset(&pool, 0, sizeof(pool));
-	}
+	for (i = 0; i < MAX_POOLS; i++)
+		if (g_pools[i] && g_pools[i]->ctx == ctx) {
+			if (g_pools[i]->live)
+				fprintf(stderr,
+					"lz4e_chunk: context destroyed with %zu pool buffers live\n",
+					g_pools[i]->live);
+			pool_release_locked(i);
+		}
 	pthread_mutex_unlock(&p_mu);
 }
 
-static int pool_init_locked(lz4e_b200_ctx *ctx, size_t pool_pages)
+/* the context this thread's chunk calls run on */
+static lz4e_b200_ctx *current_ctx_locked(void)
 {
-	if (pool.ready)
-		return 0;
+	if (t_ctx)
+		return t_ctx;
+	if (g_first_ctx)
+		return g_first_ctx;
+	return lz4e_b200_default_ctx();
+}
+
+/* the pool of ctx, created on first use; NULL when that fails */
+static struct pool *pool_get_locked(lz4e_b200_ctx *ctx, size_t pool_pages)
+{
+	struct pool *pl;
+	int i, slot = -1;
+
 	if (!ctx)
-		ctx = lz4e_b200_default_ctx();
-	if (!ctx)
-		return -ENODEV;
+		return NULL;
+	for (i = 0; i < MAX_POOLS; i++) {
+		if (g_pools[i] && g_pools[i]->ctx == ctx)
+			return g_pools[i];
+		if (!g_pools[i] && slot < 0)
+			slot = i;
+	}
+	if (slot < 0)
+		return NULL;
 	if (!pool_pages) {
 		const char *e = getenv("LZ4E_CHUNK_POOL_MB");
 		long mb = e ? atol(e) : 1024;
@@ -69,22 +113,33 @@ static int pool_init_locked(lz4e_b200_ctx *ctx, size_t pool_pages)
 			mb = 1;
 		pool_pages = (size_t)mb << (20 - PAGE_SHIFT);
 	}
-	if (lz4e_b200_arena_create(ctx, pool_pages, &pool.arena) != LZ4E_B200_OK)
-		return -ENOMEM;
-	pool.next = calloc(pool_pages, sizeof(*pool.next));
-	if (!pool.next) {
-		lz4e_b200_arena_destroy(pool.arena);
-		return -ENOMEM;
+	pl = calloc(1, sizeof(*pl));
+	if (!pl)
+		return NULL;
+	pl->next = calloc(pool_pages, sizeof(*pl->next));
+	if (!pl->next || lz4e_b200_arena_create(ctx, pool_pages, &pl->arena) != LZ4E_B200_OK) {
+		free(pl->next);
+		free(pl);
+		return NULL;
 	}
-	pool.ctx = ctx;
+	pl->ctx = ctx;
+	pl->base = (uint8_t *)lz4e_b200_arena_pages(pl->arena);
+	pl->npages = pool_pages;
 	lz4e_ctx_attach(ctx, LZ4E_ATTACH_CHUNK_POOL, 8, pool_ctx_dtor);
-	pool.base = (uint8_t *)lz4e_b200_arena_pages(pool.arena);
-	pool.npages = pool_pages;
-	pool.bump = 0;
-	pool.live = 0;
-	memset(pool.freel, 0, sizeof(pool.freel));
-	pool.ready = 1;
-	return 0;
+	g_pools[slot] = pl;
+	return pl;
+}
+
+/* the pool whose pages hold p, or NULL */
+static struct pool *pool_of_locked(const void *p)
+{
+	int i;
+
+	for (i = 0; i < MAX_POOLS; i++)
+		if (g_pools[i] && (const uint8_t *)p >= g_pools[i]->base &&
+		    (const uint8_t *)p < g_pools[i]->base + (g_pools[i]->npages << PAGE_SHIFT))
+			return g_pools[i];
+	return NULL;
 }
 
 int lz4e_chunk_setup(lz4e_b200_ctx *ctx, size_t pool_pages)
@@ -92,19 +147,28 @@ int lz4e_chunk_setup(lz4e_b200_ctx *ctx, size_t pool_pages)
 	int rc;
 
 	pthread_mutex_lock(&p_mu);
-	rc = pool_init_locked(ctx, pool_pages);
+	if (!ctx)
+		ctx = current_ctx_locked();
+	rc = !ctx ? -ENODEV : pool_get_locked(ctx, pool_pages) ? 0 : -ENOMEM;
+	if (!rc && !g_first_ctx)
+		g_first_ctx = ctx;
 	pthread_mutex_unlock(&p_mu);
 	return rc;
 }
 
+void lz4e_chunk_bind(lz4e_b200_ctx *ctx)
+{
+	t_ctx = ctx;
+}
+
 void lz4e_chunk_teardown(void)
 {
+	int i;
+
 	pthread_mutex_lock(&p_mu);
-	if (pool.ready && pool.live == 0) {
-		lz4e_b200_arena_destroy(pool.arena);
-		free(pool.next);
-		memset(&pool, 0, sizeof(pool));
-	}
+	for (i = 0; i < MAX_POOLS; i++)
+		if (g_pools[i] && g_pools[i]->live == 0)
+			pool_release_locked(i);
 	pthread_mutex_unlock(&p_mu);
 }
 
@@ -113,23 +177,25 @@ void lz4e_chunk_teardown(void)
 static void *pool_alloc(size_t bytes, int *from_pool)
 {
 	size_t pages = (bytes + PAGE_SIZE - 1) >> PAGE_SHIFT;
+	struct pool *pl;
 	void *p = NULL;
 
 	if (!pages)
 		pages = 1;
 	pthread_mutex_lock(&p_mu);
-	if (pool_init_locked(NULL, 0) == 0 && pages < POOL_CLASSES) {
-		if (pool.freel[pages]) {
-			const size_t idx = pool.freel[pages] - 1;
+	pl = pool_get_locked(current_ctx_locked(), 0);
+	if (pl && pages < POOL_CLASSES) {
+		if (pl->freel[pages]) {
+			const size_t idx = pl->freel[pages] - 1;
 
-			p = pool.base + (idx << PAGE_SHIFT);
-			pool.freel[pages] = pool.next[idx];
-		} else if (pool.bump + pages <= pool.npages) {
-			p = pool.base + (pool.bump << PAGE_SHIFT);
-			pool.bump += pages;
+			p = pl->base + (idx << PAGE_SHIFT);
+			pl->freel[pages] = pl->next[idx];
+		} else if (pl->bump + pages <= pl->npages) {
+			p = pl->base + (pl->bump << PAGE_SHIFT);
+			pl->bump += pages;
 		}
 		if (p)
-			pool.live++;
+			pl->live++;
 	}
 	pthread_mutex_unlock(&p_mu);
 	*from_pool = p != NULL;
@@ -145,19 +211,20 @@ static void *pool_alloc(size_t bytes, int *from_pool)
 static void pool_free(void *p, size_t bytes)
 {
 	size_t pages = (bytes + PAGE_SIZE - 1) >> PAGE_SHIFT;
+	struct pool *pl;
 
 	if (!p)
 		return;
 	if (!pages)
 		pages = 1;
 	pthread_mutex_lock(&p_mu);
-	if (pool.ready && (uint8_t *)p >= pool.base &&
-	    (uint8_t *)p < pool.base + (pool.npages << PAGE_SHIFT)) {
-		const size_t idx = (size_t)((uint8_t *)p - pool.base) >> PAGE_SHIFT;
+	pl = pool_of_locked(p);
+	if (pl) {
+		const size_t idx = (size_t)((uint8_t *)p - pl->base) >> PAGE_SHIFT;
 
-		pool.next[idx] = pool.freel[pages];
-		pool.freel[pages] = idx + 1;
-		pool.live--;
+		pl->next[idx] = pl->freel[pages];
+		pl->freel[pages] = idx + 1;
+		pl->live--;
 		pthread_mutex_unlock(&p_mu);
 		return;
 	}
@@ -165,21 +232,34 @@ static void pool_free(void *p, size_t bytes)
 	free(p);
 }
 
-static int in_pool(const void *p)
+/*
+ * Context a batch of chunks runs on, how many of its buffers are pool buffers
+ * of that context and how many pool buffers of it are live: the context of the
+ * pool that holds the first chunk's buffers, else this thread's.
+ */
+static lz4e_b200_ctx *batch_ctx(struct lz4e_chunk **chunks, size_t n, size_t *mine, size_t *live)
 {
-	return pool.ready && (const uint8_t *)p >= pool.base &&
-	       (const uint8_t *)p < pool.base + (pool.npages << PAGE_SHIFT);
-}
+	struct pool *pl = NULL;
+	lz4e_b200_ctx *ctx;
+	size_t i;
 
-static lz4e_b200_ctx *chunk_ctx(void)
-{
-	lz4e_b200_ctx *c;
-
+	*mine = *live = 0;
 	pthread_mutex_lock(&p_mu);
-	pool_init_locked(NULL, 0);
-	c = pool.ctx;
+	if (n)
+		pl = pool_of_locked(chunks[0]->src_buf.data);
+	if (!pl && n)
+		pl = pool_of_locked(chunks[0]->dst_buf.data);
+	if (!pl)
+		pl = pool_get_locked(current_ctx_locked(), 0);
+	ctx = pl ? pl->ctx : current_ctx_locked();
+	if (pl) {
+		for (i = 0; i < n; i++)
+			*mine += (size_t)(pool_of_locked(chunks[i]->src_buf.data) == pl) +
+				 (size_t)(pool_of_locked(chunks[i]->dst_buf.data) == pl);
+		*live = pl->live;
+	}
 	pthread_mutex_unlock(&p_mu);
-	return c ? c : lz4e_b200_default_ctx();
+	return ctx;
 }
 
 /* ---- chunks (lz4e_chunk.c:19-107 of the reference) -------------------------- */
@@ -314,7 +394,8 @@ static int chunk_batch(struct lz4e_chunk **chunks, size_t n, int *status, int op
 		       unsigned int extra_flags)
 {
 	struct call_ws w;
-	lz4e_b200_ctx *ctx = chunk_ctx();
+	size_t mine = 0, live = 0;
+	lz4e_b200_ctx *ctx = batch_ctx(chunks, n, &mine, &live);
 	size_t i;
 	int rc;
 
@@ -365,14 +446,7 @@ static int chunk_batch(struct lz4e_chunk **chunks, size_t n, int *status, int op
 		 * ask for the range to be uploaded first.  A batch that owns every
 		 * live pool buffer (the request path below) skips that. */
 		unsigned int flags = extra_flags;
-		size_t mine = 0, live;
 
-		for (i = 0; i < n; i++)
-			mine += (size_t)in_pool(chunks[i]->src_buf.data) +
-				(size_t)in_pool(chunks[i]->dst_buf.data);
-		pthread_mutex_lock(&p_mu);
-		live = pool.live;
-		pthread_mutex_unlock(&p_mu);
 		if (live > mine)
 			flags |= LZ4E_B200_F_DST_PRESERVE;
 		if (op == OP_DECOMPRESS)

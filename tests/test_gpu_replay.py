@@ -49,3 +49,15 @@ def test_replay_chunk_size_only():
     assert r["failed"] == 0 and r["mismatches"] == 0
     assert r["compressed_bytes"] == r["oracle_compressed_bytes"] > 0
     assert r["per_bio_digest_equal"] is True
+
+
+def test_replay_two_submitters_one_process():
+    """One submitter thread per GPU in ONE process (two contexts, two chunk pools, thread-bound
+    with lz4e_chunk_bind; on a one-GPU box both share the device): same checks, counters add
+    up."""
+    r = _run("--qd", "64", "--batches", "4", "--capacity-mib", "64", "--seed", "5", "--devices", "2",
+             "--arena-bios")
+    assert r["submitters"] == 2
+    assert r["failed"] == 0 and r["mismatches"] == 0
+    assert r["compressed_bytes"] == r["oracle_compressed_bytes"] > 0
+    assert r["per_bio_digest_equal"] is True

@@ -24,6 +24,7 @@
 #include <unistd.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <pthread.h>
 #include <string.h>
 #include <time.h>
 
@@ -35,10 +36,11 @@
 struct opts {
 	unsigned qd, batches, min_kib, max_kib, read_pct, seed, capacity_mib, device;
 	int arena_bios, json;
+	unsigned devices; /* > 1: one submitter thread per GPU 0 .. devices-1 in this process */
 	const char *oracle;
 };
 
-static uint32_t rng_state;
+static __thread uint32_t rng_state; /* one request stream per submitter thread */
 static uint32_t rnd(void)
 {
 	rng_state = rng_state * 1664525u + 1013904223u;
@@ -114,7 +116,7 @@ static void usage(void)
 {
 	puts("lz4e_replay [--qd 256] [--batches 64] [--min-kib 4] [--max-kib 128]\n"
 	     "            [--read-pct 30] [--capacity-mib 1024] [--seed 1] [--device 0]\n"
-	     "            [--arena-bios] [--oracle liblz4e_ref.so] [--json]");
+	     "            [--devices N] [--arena-bios] [--oracle liblz4e_ref.so] [--json]");
 }
 
 static int parse(int argc, char **argv, struct opts *o)
@@ -150,6 +152,8 @@ static int parse(int argc, char **argv, struct opts *o)
 			o->seed = (unsigned)atoi(v), i++;
 		} else if (!strcmp(a, "--device")) {
 			o->device = (unsigned)atoi(v), i++;
+		} else if (!strcmp(a, "--devices")) {
+			o->devices = (unsigned)atoi(v), i++;
 		} else if (!strcmp(a, "--oracle")) {
 			o->oracle = v, i++;
 		} else {
@@ -162,9 +166,17 @@ static int parse(int argc, char **argv, struct opts *o)
 	return 0;
 }
 
-int main(int argc, char **argv)
+struct result {
+	int rc;
+	double gbs, wgbs, p50, p99, pmax;
+	uint64_t wreqs, rreqs, wbytes, rbytes, cbytes, obytes, launches;
+	unsigned failed, bad;
+	int digest; /* -1 no oracle, 0 differs, 1 equal */
+};
+
+/* one submitter: its own context, chunk pool, stand-in device and request stream */
+static int run(struct opts o, struct result *res)
 {
-	struct opts o = { 256, 64, 4, 128, 30, 1, 1024, 0, 0, 0, NULL };
 	lz4e_b200_ctx *ctx = NULL;
 	lz4e_b200_arena *arena = NULL;
 	struct lz4e_dev *dev;
@@ -180,12 +192,8 @@ int main(int argc, char **argv)
 	void *ref_wrk = NULL;
 	struct lz4e_stats ws, rs;
 
-	signal(SIGBUS, on_fatal);
-	signal(SIGSEGV, on_fatal);
-	if (parse(argc, argv, &o)) {
-		usage();
-		return 2;
-	}
+	memset(res, 0, sizeof(*res));
+	res->rc = 3;
 	rng_state = o.seed * 2654435761u + 12345u;
 	capacity = (uint64_t)o.capacity_mib << 20;
 	max_pages = o.max_kib / 4;
@@ -194,6 +202,8 @@ int main(int argc, char **argv)
 			lz4e_b200_strerror(NULL));
 		return 3; /* no CPU fallback */
 	}
+	/* this thread's chunk and request-path calls run on this context */
+	lz4e_chunk_bind(ctx);
 	/* chunk pool: src + dst buffer per outstanding write, page-rounded */
 	if (lz4e_chunk_setup(ctx, (size_t)o.qd * (2 * max_pages + 3) + 64)) {
 		fprintf(stderr, "lz4e_replay: chunk pool: %s\n", lz4e_b200_strerror(ctx));
@@ -349,38 +359,116 @@ int main(int argc, char **argv)
 			(unsigned long long)oracle_bytes);
 		bad++;
 	}
-	{
-		const double gbs = (double)(wbytes + rbytes) / (t_all * 1e-3) / 1e9;
-		const double wgbs = (double)wbytes / (t_all * 1e-3) / 1e9;
-		const uint64_t cbytes = lz4e_dev_compressed_bytes(dev);
-
-		qsort(lat, o.batches, sizeof(*lat), cmp_double);
-		printf("%s\"workload\": \"chunk-layer replay: QD%u, %u batches, %u-%u KiB, %u%% reads, "
-		       "%s bio pages\", \"gbs\": %.3f, \"write_gbs\": %.3f, \"batch_ms_p50\": %.3f, "
-		       "\"batch_ms_p99\": %.3f, \"batch_ms_max\": %.3f, \"write_reqs\": %llu, "
-		       "\"read_reqs\": %llu, \"write_bytes\": %llu, \"read_bytes\": %llu, "
-		       "\"compressed_bytes\": %llu, \"oracle_compressed_bytes\": %s%llu, \"per_bio_digest_equal\": %s, "
-		       "\"failed\": %u, \"mismatches\": %u, \"gpu_launches\": %llu%s\n",
-		       "{", o.qd, o.batches, o.min_kib, o.max_kib, o.read_pct,
-		       o.arena_bios ? "arena (pinned, mirrored)" : "pageable (bounced)", gbs, wgbs,
-		       pct(lat, o.batches, 0.50), pct(lat, o.batches, 0.99), lat[o.batches - 1],
-		       (unsigned long long)wreqs, (unsigned long long)rreqs,
-		       (unsigned long long)wbytes, (unsigned long long)rbytes,
-		       (unsigned long long)cbytes, "", (unsigned long long)oracle_bytes,
-		       !ref_compress ? "null"
-		       : oracle_digest == lz4e_dev_compressed_digest(dev) ? "true" : "false",
-		       failed, bad,
-		       (unsigned long long)(lz4e_b200_kernel_launches(ctx) - launches0), "}");
-	}
+	qsort(lat, o.batches, sizeof(*lat), cmp_double);
+	res->gbs = (double)(wbytes + rbytes) / (t_all * 1e-3) / 1e9;
+	res->wgbs = (double)wbytes / (t_all * 1e-3) / 1e9;
+	res->p50 = pct(lat, o.batches, 0.50);
+	res->p99 = pct(lat, o.batches, 0.99);
+	res->pmax = lat[o.batches - 1];
+	res->wreqs = wreqs, res->rreqs = rreqs, res->wbytes = wbytes, res->rbytes = rbytes;
+	res->cbytes = lz4e_dev_compressed_bytes(dev);
+	res->obytes = oracle_bytes;
+	res->digest = !ref_compress ? -1 : oracle_digest == lz4e_dev_compressed_digest(dev);
+	res->failed = failed, res->bad = bad;
+	res->launches = lz4e_b200_kernel_launches(ctx) - launches0;
 	for (i = 0; i < o.qd; i++)
 		free(slots[i].vecs);
 	lz4e_dev_destroy(dev);
-	lz4e_chunk_teardown();
-	if (arena)
-		lz4e_b200_arena_destroy(arena);
-	else
+	lz4e_chunk_bind(NULL);
+	/* the context takes its chunk pool and arenas with it */
+	if (!arena)
 		free(pages_mem);
 	lz4e_b200_ctx_destroy(ctx);
 	free(shadow);
-	return bad || failed ? 1 : 0;
+	res->rc = bad || failed ? 1 : 0;
+	return res->rc;
+}
+
+struct job {
+	struct opts o;
+	struct result r;
+};
+
+static void *job_main(void *p)
+{
+	struct job *j = p;
+
+	run(j->o, &j->r);
+	return NULL;
+}
+
+int main(int argc, char **argv)
+{
+	struct opts o = { 256, 64, 4, 128, 30, 1, 1024, 0, 0, 0, 1, NULL };
+	struct job jobs[16];
+	pthread_t th[16];
+	struct result t;
+	unsigned d, n;
+	double t0, wall;
+
+	signal(SIGBUS, on_fatal);
+	signal(SIGSEGV, on_fatal);
+	if (parse(argc, argv, &o) || o.devices < 1 || o.devices > 16) {
+		usage();
+		return 2;
+	}
+	n = o.devices;
+	for (d = 0; d < n; d++) {
+		jobs[d].o = o;
+		if (n > 1) {
+			/* submitter d on GPU d; with fewer GPUs than submitters they
+			 * share (each still has its own context and pool) */
+			const int ndev = lz4e_b200_device_count();
+
+			jobs[d].o.device = ndev > 0 ? d % (unsigned)ndev : d;
+			jobs[d].o.seed = o.seed + d;
+		}
+	}
+	t0 = now_ms();
+	for (d = 1; d < n; d++)
+		pthread_create(&th[d], NULL, job_main, &jobs[d]);
+	job_main(&jobs[0]);
+	for (d = 1; d < n; d++)
+		pthread_join(th[d], NULL);
+	wall = now_ms() - t0;
+	/* throughput and counters add up, latencies are the slowest submitter's */
+	t = jobs[0].r;
+	for (d = 1; d < n; d++) {
+		const struct result *r = &jobs[d].r;
+
+		if (r->rc > t.rc)
+			t.rc = r->rc;
+		t.gbs += r->gbs, t.wgbs += r->wgbs;
+		if (r->p50 > t.p50)
+			t.p50 = r->p50;
+		if (r->p99 > t.p99)
+			t.p99 = r->p99;
+		if (r->pmax > t.pmax)
+			t.pmax = r->pmax;
+		t.wreqs += r->wreqs, t.rreqs += r->rreqs, t.wbytes += r->wbytes, t.rbytes += r->rbytes;
+		t.cbytes += r->cbytes, t.obytes += r->obytes, t.launches += r->launches;
+		t.failed += r->failed, t.bad += r->bad;
+		if (r->digest < t.digest)
+			t.digest = r->digest;
+	}
+	if (t.rc == 3) {
+		fprintf(stderr, "lz4e_replay: set-up failed (no CUDA device or out of memory)\n");
+		return 3;
+	}
+	printf("{\"workload\": \"chunk-layer replay: QD%u, %u batches, %u-%u KiB, %u%% reads, "
+	       "%s bio pages%s\", \"gbs\": %.3f, \"write_gbs\": %.3f, \"batch_ms_p50\": %.3f, "
+	       "\"batch_ms_p99\": %.3f, \"batch_ms_max\": %.3f, \"write_reqs\": %llu, "
+	       "\"read_reqs\": %llu, \"write_bytes\": %llu, \"read_bytes\": %llu, "
+	       "\"compressed_bytes\": %llu, \"oracle_compressed_bytes\": %llu, "
+	       "\"per_bio_digest_equal\": %s, \"failed\": %u, \"mismatches\": %u, "
+	       "\"gpu_launches\": %llu, \"submitters\": %u, \"wall_ms\": %.1f}\n",
+	       o.qd, o.batches, o.min_kib, o.max_kib, o.read_pct,
+	       o.arena_bios ? "arena (pinned, mirrored)" : "pageable (bounced)",
+	       n > 1 ? ", one submitter thread per GPU in one process" : "", t.gbs, t.wgbs, t.p50,
+	       t.p99, t.pmax, (unsigned long long)t.wreqs, (unsigned long long)t.rreqs,
+	       (unsigned long long)t.wbytes, (unsigned long long)t.rbytes,
+	       (unsigned long long)t.cbytes, (unsigned long long)t.obytes,
+	       t.digest < 0 ? "null" : t.digest ? "true" : "false", t.failed, t.bad,
+	       (unsigned long long)t.launches, n, wall);
+	return t.rc;
 }
