@@ -81,15 +81,17 @@ typedef union {
  *             output capacity too small).  On success the iterators are left
  *             where the reference leaves them: *srcIter at the last match-search
  *             position, *dstIter at the first byte of the final literal run.
- *             On a 0 return the reference leaves both iterators somewhere in
- *             the middle of the block and a partial prefix in dst
- *             (lz4e_compress.c:358-363, :425-430, :509 return from inside the
- *             loop).  Here a 0 return leaves *srcIter / *dstIter UNCHANGED and
- *             the destination bytes unspecified (some prefix may have been
- *             written, never beyond dstIter->bi_size).  That is safe for the
- *             reference's only caller: lz4e_chunk_compress_ext works on copies
- *             of the iterators and discards them and the buffer on failure
- *             (lz4e_bdev/lz4e_chunk.c:143-155).
+ *             On a 0 return caused by the output capacity the reference
+ *             returns from inside its loop (lz4e_compress.c:358-363, :425-430,
+ *             :509) with both iterators mid-way and a partial prefix in dst;
+ *             the same state is produced here: *srcIter / *dstIter stand where
+ *             the failing check found them and the destination holds the
+ *             reference's bytes up to *dstIter.  Two things are unspecified,
+ *             as they are garbage in the reference too: the token byte of the
+ *             sequence in progress (never stored on these paths; it holds
+ *             what the previous 4-byte length store or the caller left there)
+ *             and the bytes behind *dstIter.  A block rejected up front
+ *             (size, bvec count) leaves the iterators untouched, as there.
  */
 int LZ4E_compress_default(const struct bio_vec *src, struct bio_vec *dst,
 			  struct bvec_iter *srcIter, struct bvec_iter *dstIter,

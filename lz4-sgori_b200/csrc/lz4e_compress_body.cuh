@@ -178,6 +178,62 @@ LZ4E_DEV void lz4e_put_run(uint8_t *p, uint32_t count, uint32_t last,
 }
 
 /*
+ * limitedOutput failure inside a sequence (lz4e_compress.c:358-363 and
+ * :425-430).  The reference returns 0 with its iterators where they were and
+ * with what it had stored so far; callers that look at *dstIter after a 0 see
+ * that state, so it is reproduced: everything before the sequence is flushed,
+ * and for the second check (`second`) the literal length bytes, the literals
+ * and the offset are stored too.  The token byte of the sequence is never
+ * written by the reference on these paths and is left alone here.  Cold and
+ * out of line: the encoder's emit path only tests for it.
+ */
+template <bool DIRECT>
+LZ4E_DEV_NOINLINE void lz4e_compress_overflow(uint8_t *cur0, uint8_t *base, uint32_t win,
+					      const struct lz4e_b200_dev_bvec *dv, uint32_t ddone,
+					      const uint8_t *d, uint32_t op, uint32_t anchor,
+					      uint32_t lit, uint32_t lit_ext, uint32_t off,
+					      bool second, uint32_t lane)
+{
+	/* everything by value: taking the address of the encoder's staging state
+	 * would move it from registers to local memory on the hot path */
+	lz4e_cursor c = { dv, ddone };
+
+	if (DIRECT) {
+		uint8_t *o = cur0 + op + 1u;
+
+		if (!second)
+			return;
+		if (lit_ext)
+			lz4e_put_run(o, lit_ext, (lit - 15u) % 255u, lane);
+		o += lit_ext;
+		lz4e_copy<32>(o, d + anchor, lit, lane);
+		if (lane < 2u)
+			o[lit + lane] = (uint8_t)(lane ? off >> 8 : off);
+		return;
+	}
+	lz4e_syncwarp(LZ4E_FULL);
+	lz4e_scatter<32>(c, cur0, op - win, lane);
+	lz4e_syncwarp(LZ4E_FULL);
+	if (!second)
+		return;
+	lz4e_cursor_skip(c, 1u); /* the token byte */
+	for (uint32_t left = lit_ext; left;) {
+		const uint32_t part = left < 512u ? left : 512u;
+
+		lz4e_put_run(base, part, part == left ? (lit - 15u) % 255u : 255u, lane);
+		lz4e_syncwarp(LZ4E_FULL);
+		lz4e_scatter<32>(c, base, part, lane);
+		lz4e_syncwarp(LZ4E_FULL);
+		left -= part;
+	}
+	lz4e_scatter<32>(c, d + anchor, lit, lane);
+	if (lane < 2u)
+		base[lane] = (uint8_t)(lane ? off >> 8 : off);
+	lz4e_syncwarp(LZ4E_FULL);
+	lz4e_scatter<32>(c, base, 2u, lane);
+}
+
+/*
  * The hash table in shared memory.  Plain form: one TABT per entry.  Packed
  * form (P12, blocks of at most 4 KiB in byU16 mode): positions fit 12 bits, so
  * the 8192 entries take 12 KiB instead of 16 — low bytes in [0, 8192), high
@@ -598,8 +654,19 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 
 					if (limited &&
 					    (op + 1u + lit + 8u + lit / 255u > cap ||
-					     op + 1u + lit_ext + lit + 2u + 6u + (mc >> 8) > cap))
+					     op + 1u + lit_ext + lit + 2u + 6u + (mc >> 8) > cap)) {
+						/* :358-363 is not on the path of an immediate match
+						 * (goto _next_match, :489-492): ip == anchor there */
+						const bool first = ip != anchor &&
+								   op + 1u + lit + 8u + lit / 255u > cap;
+
+						lz4e_compress_overflow<DIRECT>(st.cur0, st.base, st.win, st.dst.v,
+									       st.dst.done, d, op, anchor, lit,
+									       lit_ext, off, !first, lane);
+						src_end = first ? ip - back : ip + 4u + ml;
+						dst_end = first ? op + 1u : op + 1u + lit_ext + lit + 2u;
 						return 0;
+					}
 
 					bool stream = false;
 
@@ -690,8 +757,13 @@ LZ4E_DEV int32_t lz4e_compress_encode(const lz4e_compress_args &a,
 			const uint32_t run = n - anchor;
 			const uint32_t ext = run >= 15u ? (run - 15u) / 255u + 1u : 0u;
 
-			if (limited && op + run + 1u + (run + 240u) / 255u > cap)
+			if (limited && op + run + 1u + (run + 240u) / 255u > cap) {
+				/* :505-509: everything before the last run is out */
+				lz4e_compress_overflow<DIRECT>(st.cur0, st.base, st.win, st.dst.v, st.dst.done,
+						       d, op, anchor, 0, 0, 0, false, lane);
+				dst_end = op;
 				return 0;
+			}
 			if (!DIRECT && op - st.win + 1u + ext > st.cap)
 				lz4e_stage_flush(st, op, a.out_cap, lane);
 			uint8_t *o = st.cur0 + (op - st.win);
@@ -896,8 +968,10 @@ done:
 	if (lane == 0) {
 		a.rets[b] = ret;
 		if (a.ends) {
-			a.ends[b].src_pos = ret ? src_end : 0;
-			a.ends[b].dst_pos = ret ? dst_end : 0;
+			/* also after a 0 return: the reference leaves its iterators
+			 * where the failing check found them */
+			a.ends[b].src_pos = src_end;
+			a.ends[b].dst_pos = dst_end;
 		}
 	}
 	/* the next block reuses this warp's shared memory */

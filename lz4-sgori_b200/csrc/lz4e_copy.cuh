@@ -166,6 +166,22 @@ LZ4E_DEV uint8_t *lz4e_cursor_addr(const lz4e_cursor &c)
 	return p;
 }
 
+/* move the cursor n bytes forward; the bytes must exist */
+LZ4E_DEV void lz4e_cursor_skip(lz4e_cursor &c, uint32_t n)
+{
+	while (n) {
+		const uint32_t room = c.v->len - c.done;
+
+		if (n < room) {
+			c.done += n;
+			return;
+		}
+		n -= room;
+		c.v++;
+		c.done = 0;
+	}
+}
+
 /* copy `len` bytes from linear memory `src` to the SG stream at cursor c */
 template <int W>
 LZ4E_DEV void lz4e_scatter(lz4e_cursor &c, const uint8_t *src, uint32_t len,

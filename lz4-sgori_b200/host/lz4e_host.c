@@ -798,9 +798,11 @@ static int lane_finish(lz4e_b200_ctx *ctx, struct host_ws *ws, struct lane *ln,
 		struct lz4e_b200_req *q = &ln->reqs[i];
 
 		q->ret = rets[i];
-		if (!decompress && rets[i] > 0 && !(flags & LZ4E_B200_F_KEEP_ITERS)) {
+		if (!decompress && rets[i] >= 0 && !(flags & LZ4E_B200_F_KEEP_ITERS)) {
 			/* leave the iterators where the reference does,
-			 * lz4e_compress.c:304-305 and :528-529 */
+			 * lz4e_compress.c:304-305 and :528-529 — also after a 0
+			 * return (:363, :430, :509), where they stay at the failing
+			 * check; blocks rejected up front report 0/0 */
 			lz4e_bvec_iter_advance(q->src, q->src_iter, ends[i].src_pos);
 			lz4e_bvec_iter_advance(q->dst, q->dst_iter, ends[i].dst_pos);
 		}

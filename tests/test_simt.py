@@ -59,22 +59,39 @@ def test_compress_body_matches_oracle(simt, ref_lib, out_cap, gin):
 
 
 @pytest.mark.parametrize("out_cap", [1024, 64])
-def test_compress_body_limited_output(simt, ref_lib, out_cap):
-    datas = [common.synth(4096, c, 77 + c) for c in range(4)] * 3
+@pytest.mark.parametrize("sg_dst", [False, True])
+def test_compress_body_limited_output(simt, ref_lib, out_cap, sg_dst):
+    """limitedOutput (lz4e_compress.c:358-363, :425-430, :509): return values, and after a 0
+    return the iterator positions and the destination prefix up to *dstIter the reference leaves
+    (the token byte of the sequence in progress is garbage on both sides: <= 1 byte differs)."""
+    if sg_dst and out_cap == 64:
+        pytest.skip("out_cap 64 selects the in-place kernels: linear destinations only")
+    datas = [common.synth(4096, c, 77 + c) for c in range(4)] * 6
     specs = [sg.segs_single(4096)] * len(datas)
     src = _host_layout(specs, datas)
     full = _host_layout([sg.segs_single(sg.compress_bound(4096))] * len(datas))
     sizes, _ = common.oracle.compress_batch(ref_lib, src.bvecs, src.first, src.iters,
                                             full.bvecs, full.first, full.iters)
-    caps = [int(s) + d for s, d in zip(sizes, [0, -1, -7, 5] * 3)]  # exact fit, too small, ...
-    dspecs = [sg.segs_single(max(c, 1)) for c in caps]
+    deltas = [0, -1, -7, 5] * 3 + [-2, -3, -5, -6, -9, -12, -40, -100, -300, -1000, -1500, -16]
+    caps = [max(int(s) + d if d > -1000 else int(s) // (2 if d == -1000 else 3), 1)
+            for s, d in zip(sizes, deltas)]
+    dspecs = [sg.segs_odd(c, 5, i) if sg_dst and c > 64 else sg.segs_single(c)
+              for i, c in enumerate(caps)]
     dst = _host_layout(dspecs)
-    rets, _, faults = emu.compress(simt, src, dst, in_cap=4096, out_cap=out_cap)
-    ref_dst, (ref_rets, _) = common.oracle_compress(ref_lib, src, dspecs)
+    dst.arena.mem[:] = 0xEE
+    rets, ends, faults = emu.compress(simt, src, dst, in_cap=4096, out_cap=out_cap)
+    ref_dst, (ref_rets, _, so, do) = common.oracle_compress(ref_lib, src, dspecs, want_iters=True)
     assert faults == 0
     assert np.array_equal(rets, ref_rets)
+    assert (rets == 0).sum() >= 12
     for b in range(len(datas)):
         assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
+        dp = caps[b] - int(do[b]["bi_size"])
+        assert int(ends[b]["src_pos"]) == 4096 - int(so[b]["bi_size"]), b
+        assert int(ends[b]["dst_pos"]) == dp, b
+        if rets[b] == 0 and dp:
+            got, want = dst.read_block(b, dp), ref_dst.read_block(b, dp)
+            assert int((got != want).sum()) <= 1, b
 
 
 @pytest.mark.parametrize("out_cap", [1024, 4352, 64])
