@@ -151,6 +151,43 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 			   struct lz4e_b200_dev_end *ends);
 
 /*
+ * lz4e_b200_compress_dev for callers that must not allocate device memory
+ * inside the call (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the
+ * reference.
+ *
+ * Same arguments, same results (rets, ends, destination bytes) as
+ * lz4e_b200_compress_dev.  It always runs the global-input compress kernel
+ * (each warp gathers its block into a linear slot in global memory), and the
+ * kernel's scratch — the work-queue counter and the input slots — lives in ONE
+ * fixed array of LZ4E_B200_STATIC_SCRATCH_BYTES in the library's device image
+ * (every GPU that loads the library holds it until the process exits) instead
+ * of buffers the context grows with cudaMalloc.  The call itself makes no
+ * cudaMalloc / cudaFree; the first call on a device looks the array's device
+ * address up once (cudaGetSymbolAddress).
+ *
+ * Limits: max_in_bytes <= LZ4E_B200_STATIC_MAX_BLOCK, else LZ4E_B200_EINVAL
+ * with a message in lz4e_b200_strerror(); any nblocks (the number of resident
+ * warps is cut to the slots that fit the array: 127 slots at 64 KiB blocks, so
+ * large blocks run with less parallelism than through lz4e_b200_compress_dev).
+ * All calls — every context, every stream of a device — share the array: the
+ * counter is cleared on the call's stream before the kernel, slots need no
+ * clearing (each block overwrites what it reads), and two calls that overlap
+ * on the GPU (different streams without an event between them) race on it and
+ * produce garbage.  Serialise them.
+ */
+#define LZ4E_B200_STATIC_SCRATCH_BYTES (8u << 20)
+#define LZ4E_B200_STATIC_MAX_BLOCK 65536u
+int lz4e_b200_compress_dev_static(lz4e_b200_ctx *ctx, void *stream,
+				  const struct lz4e_b200_dev_bvec *src_bvecs,
+				  const struct lz4e_b200_dev_iter *src_iters,
+				  const struct lz4e_b200_dev_bvec *dst_bvecs,
+				  const struct lz4e_b200_dev_iter *dst_iters,
+				  uint32_t nblocks, uint32_t max_in_bytes,
+				  uint32_t flags, int32_t *rets,
+				  struct lz4e_b200_dev_end *ends);
+
+/*
  * LZ4E decompression (lz4e/lz4e_decompress.c:462-470 semantics on the
  * linearised bytes) with scatter-gather source and destination.
  *  src_iters[b].bi_size  compressed size,  dst_iters[b].bi_size  capacity

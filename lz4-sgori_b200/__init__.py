@@ -70,6 +70,7 @@ def lib():
         "lz4e_b200_kernel_launches": (u64, [vp]),
         "lz4e_b200_sync": (i32, [vp, vp]),
         "lz4e_b200_compress_dev": (i32, [vp, vp, vp, vp, vp, vp, u32, u32, u32, vp, vp]),
+        "lz4e_b200_compress_dev_static": (i32, [vp, vp, vp, vp, vp, vp, u32, u32, u32, vp, vp]),
         "lz4e_b200_decompress_dev": (i32, [vp, vp, vp, vp, vp, vp, u32, u32, u32, u32, vp]),
         "lz4e_b200_compress_compact_dev": (i32, [vp, vp, vp, vp, vp, u32, u32, u64, u32, u32,
                                                  u32, vp, vp]),
@@ -187,6 +188,14 @@ class Context:
         self.check(lib().lz4e_b200_compress_dev(self.h, _p(stream), _p(sbv), _p(sit), _p(dbv),
                                                 _p(dit), nblocks, max_in, flags, _p(rets),
                                                 _p(ends)), "compress_dev")
+
+    def compress_dev_static(self, sbv, sit, dbv, dit, nblocks, max_in, rets, ends=None, flags=0,
+                            stream=None):
+        """compress_dev with the kernel's scratch in the library's fixed device array: no
+        allocation inside the call (include/lz4e_b200.h)."""
+        self.check(lib().lz4e_b200_compress_dev_static(self.h, _p(stream), _p(sbv), _p(sit),
+                                                       _p(dbv), _p(dit), nblocks, max_in, flags,
+                                                       _p(rets), _p(ends)), "compress_dev_static")
 
     def decompress_dev(self, sbv, sit, dbv, dit, nblocks, max_in, max_out, rets, flags=0,
                        stream=None):

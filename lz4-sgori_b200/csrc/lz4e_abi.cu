@@ -1033,3 +1033,136 @@ void lz4e_b200_shard_range(uint64_t nblocks, uint32_t rank, uint32_t world,
 }
 
 } /* extern "C" */
+
+/* ---- compress without allocations ---------------------------------------- */
+/*
+ * Scratch of lz4e_b200_compress_dev_static (include/lz4e_b200.h): one array in
+ * the library's device image, shared by every call on a device.
+ *   [0, 4)      work-queue counter of the persistent warps (cleared per call)
+ *   [256, end)  input slots of the global-input compress kernel, one per
+ *               resident warp; the last 256 bytes stay free (the encoder's
+ *               unguarded word loads may read a little past a block)
+ * In host code `g_static_scratch` is only a handle for the symbol: the device
+ * address comes from cudaGetSymbolAddress, once per device, with that device
+ * current.
+ */
+#define STATIC_HEAD 256u
+#define STATIC_MAX_DEVICES 64
+static __device__ __align__(256) uint8_t g_static_scratch[LZ4E_B200_STATIC_SCRATCH_BYTES];
+static uint8_t *g_static_ptr[STATIC_MAX_DEVICES];
+static std::mutex g_static_mu;
+
+/* device address of the array on ctx's device (which is current) */
+static uint8_t *static_scratch(lz4e_b200_ctx *ctx)
+{
+	std::lock_guard<std::mutex> lk(g_static_mu);
+
+	if (ctx->device < 0 || ctx->device >= STATIC_MAX_DEVICES) {
+		set_err(ctx, "static scratch: device %d outside 0..%d", ctx->device,
+			STATIC_MAX_DEVICES - 1);
+		return nullptr;
+	}
+	if (!g_static_ptr[ctx->device]) {
+		void *p = nullptr;
+		const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+
+		if (e != cudaSuccess || !p) {
+			set_err(ctx, "cudaGetSymbolAddress(static scratch) failed: %s",
+				cudaGetErrorString(e));
+			return nullptr;
+		}
+		g_static_ptr[ctx->device] = (uint8_t *)p;
+	}
+	return g_static_ptr[ctx->device];
+}
+
+extern "C" int lz4e_b200_compress_dev_static(lz4e_b200_ctx *ctx, void *stream,
+					     const struct lz4e_b200_dev_bvec *src_bvecs,
+					     const struct lz4e_b200_dev_iter *src_iters,
+					     const struct lz4e_b200_dev_bvec *dst_bvecs,
+					     const struct lz4e_b200_dev_iter *dst_iters,
+					     uint32_t nblocks, uint32_t max_in_bytes,
+					     uint32_t flags, int32_t *rets,
+					     struct lz4e_b200_dev_end *ends)
+{
+	lz4e_compress_args a;
+	cudaStream_t s;
+	uint8_t *scratch;
+	int grid = 0;
+	size_t smem = 0;
+
+	if (!ctx)
+		return LZ4E_B200_ENODEV;
+	if (nblocks == 0)
+		return LZ4E_B200_OK;
+	if (max_in_bytes > LZ4E_B200_STATIC_MAX_BLOCK) {
+		set_err(ctx, "lz4e_b200_compress_dev_static: max_in_bytes %u is above the %u "
+			     "bytes its fixed %u-byte scratch array serves; use "
+			     "lz4e_b200_compress_dev",
+			max_in_bytes, (unsigned)LZ4E_B200_STATIC_MAX_BLOCK,
+			(unsigned)LZ4E_B200_STATIC_SCRATCH_BYTES);
+		return LZ4E_B200_EINVAL;
+	}
+	cudaSetDevice(ctx->device);
+	scratch = static_scratch(ctx);
+	if (!scratch)
+		return LZ4E_B200_EIO;
+	std::lock_guard<std::mutex> launch_lock(g_launch_mu);
+	s = pick(ctx, stream);
+	a.src_bvecs = src_bvecs;
+	a.src_iters = src_iters;
+	a.dst_bvecs = dst_bvecs;
+	a.dst_iters = dst_iters;
+	a.rets = rets;
+	a.ends = ends;
+	a.work_counter = (uint32_t *)scratch;
+	a.faults = ctx->d_ctl + CTL_FAULTS; /* the context's own word, made at create time */
+	a.nblocks = nblocks;
+	a.order = nullptr; /* the size-ordered queue needs a buffer per batch */
+	a.tma = 0;
+	a.table_bytes = (flags & LZ4E_B200_DEV_NO_BYU16) ? 8192u : 16384u;
+	a.in_cap = (max_in_bytes + 15u) & ~15u;
+	if (a.in_cap < 16)
+		a.in_cap = 16;
+	{
+		const uint32_t bound = max_in_bytes + max_in_bytes / 255u + 16u;
+
+		a.out_cap = bound <= 4352u ? ((bound + 15u) & ~15u) + 16u : 1024u;
+		if (a.out_cap < 1024u)
+			a.out_cap = 1024u;
+		if (flags & LZ4E_B200_DEV_DST_LINEAR)
+			a.out_cap = 64u;
+	}
+	const int direct = (flags & LZ4E_B200_DEV_DST_LINEAR) ? 1 : 0;
+
+	a.in_scratch = nullptr;
+	a.in_stride = 0;
+	if (lz4e_compress_plan(&a, direct, 1, ctx->sm_count, ctx->gin_per_sm, &grid, &smem)) {
+		set_err(ctx, "compress launch plan failed: %s",
+			cudaGetErrorString(cudaGetLastError()));
+		return LZ4E_B200_EIO;
+	}
+	a.in_stride = ((a.in_cap + 63u) & ~255u) + 256u;
+	{
+		/* no more resident warps than slots in the array */
+		const size_t slots =
+			((size_t)LZ4E_B200_STATIC_SCRATCH_BYTES - STATIC_HEAD - 256u) / a.in_stride;
+
+		if ((size_t)grid * a.warps > slots)
+			grid = (int)(slots / a.warps);
+		if (grid < 1) {
+			set_err(ctx, "static scratch holds %zu slots, one CTA needs %u", slots,
+				a.warps);
+			return LZ4E_B200_EINVAL;
+		}
+	}
+	a.in_scratch = scratch + STATIC_HEAD;
+	/* the array keeps what the last call left: the counter must start at 0 */
+	CU(ctx, cudaMemsetAsync(scratch, 0, STATIC_HEAD, s));
+	if (lz4e_launch_compress(&a, direct, 1, grid, smem, s)) {
+		set_err(ctx, "compress launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+		return LZ4E_B200_EIO;
+	}
+	ctx->launches++;
+	return LZ4E_B200_OK;
+}
