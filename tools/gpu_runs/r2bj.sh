@@ -1,0 +1,5 @@
+set -x
+timeout 900 python bench.py > gpurun_out/r2bj_bench.json 2> gpurun_out/r2bj_bench.err
+timeout 900 python bench.py --impl reference > gpurun_out/r2bj_ref.json 2> gpurun_out/r2bj_ref.err
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/r2bj_smoke.log 2>&1
+tail -n 2 gpurun_out/r2bj_smoke.log
