@@ -63,6 +63,7 @@ struct lz4e_b200_ctx {
 	int dvariant; /* LZ4E_DV_*: which decoder; -1 auto */
 	int dorder;   /* cost-ordered work queue from this many blocks on; 0 = never */
 	int wave_min; /* blocks above 8 KiB: wave decoder from this many blocks on */
+	int lane_per_sm; /* lane-per-block decoder: CTAs per SM (0: as many as fit) */
 	int wave_serial; /* wave decoder: sequence-serial copy from this many bytes per sequence */
 	int p12;      /* compress: packed 12-bit table for blocks <= 4 KiB */
 	int tma;      /* compress: TMA bulk staging of the input (shared-memory kernels) */
@@ -173,6 +174,9 @@ int lz4e_b200_ctx_create(int device, lz4e_b200_ctx **out)
 	ctx->wave_min = 0;
 	if (const char *e = getenv("LZ4E_B200_WAVE_MIN"))
 		ctx->wave_min = atoi(e);
+	ctx->lane_per_sm = 0;
+	if (const char *e = getenv("LZ4E_B200_LANE_PER_SM"))
+		ctx->lane_per_sm = atoi(e);
 	ctx->dorder = 2048;
 	if (const char *e = getenv("LZ4E_B200_DORDER"))
 		ctx->dorder = atoi(e);
@@ -263,6 +267,8 @@ int lz4e_b200_ctx_tune(lz4e_b200_ctx *ctx, const char *key, int value)
 		ctx->dorder = value;
 	else if (!strcmp(key, "wave_min"))
 		ctx->wave_min = value;
+	else if (!strcmp(key, "lane_per_sm"))
+		ctx->lane_per_sm = value;
 	else if (!strcmp(key, "wave_serial"))
 		ctx->wave_serial = value;
 	else if (!strcmp(key, "p12"))
@@ -910,6 +916,13 @@ int lz4e_b200_decompress_dev(lz4e_b200_ctx *ctx, void *stream,
 			return LZ4E_B200_ENOMEM;
 		}
 		a.scratch_stride = stride;
+	}
+	if (group == 1 && ctx->lane_per_sm > 0) {
+		/* fewer resident lanes: each keeps more of its block in L2 */
+		const int cap = ctx->lane_per_sm * ctx->sm_count;
+
+		if (grid_limit == 0 || grid_limit > cap)
+			grid_limit = cap;
 	}
 	a.work_counter = next_counter(ctx, s);
 	if (lz4e_launch_decompress(&a, group, stage, variant, ctx->sm_count, s, grid_limit,
