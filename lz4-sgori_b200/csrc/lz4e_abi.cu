@@ -654,6 +654,11 @@ int lz4e_b200_compress_dev(lz4e_b200_ctx *ctx, void *stream,
 		a.out_cap = bound <= 4352u ? ((bound + 15u) & ~15u) + 16u : 1024u;
 		if (a.out_cap < 1024u)
 			a.out_cap = 1024u;
+		/* the window holds any length run by itself: one length byte per
+		 * 255 bytes of a literal run or match, 4 KiB for 1 MiB blocks,
+		 * 64 KiB for 16 MiB ones (blocks up to 255 KiB: the 1 KiB above) */
+		if (a.out_cap < ((max_in_bytes / 255u + 20u + 15u) & ~15u))
+			a.out_cap = (max_in_bytes / 255u + 20u + 15u) & ~15u;
 		/* linear destinations are written in place: no staging, more
 		 * resident warps (4 KiB blocks: 9 -> 11 per SM) */
 		if (flags & LZ4E_B200_DEV_DST_LINEAR)

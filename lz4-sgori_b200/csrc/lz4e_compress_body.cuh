@@ -63,7 +63,8 @@ struct lz4e_compress_args {
 	uint32_t nblocks;
 	uint32_t table_bytes; /* 16384, or 8192 when no block can select byU16 */
 	uint32_t in_cap;  /* bytes of input staging (multiple of 16) */
-	uint32_t out_cap; /* bytes of output staging (multiple of 16, >= 1024) */
+	uint32_t out_cap; /* bytes of output staging (multiple of 16, >= 1024 and
+			   * >= in_cap / 255 + 20; 64 = written in place) */
 	/* GIN kernels only: the block is gathered into a linear slot in global
 	 * memory (one slot per resident warp) and read back through L1, so that
 	 * shared memory holds just the hash table and large blocks no longer
@@ -816,7 +817,10 @@ LZ4E_DEV void lz4e_compress_block(const lz4e_compress_args &a, uint32_t b,
 
 	if (n > LZ4E_K_MAX_INPUT) /* lz4e_compress.c:245-248 */
 		goto done;
-	if (n > a.in_cap) {
+	/* the staging window must hold the longest length run of a block by itself
+	 * (token or offset plus one length byte per 255 bytes, lz4e_compress.c:
+	 * 365-377, :432-446, :511-522): the launch sizes out_cap from in_cap */
+	if (n > a.in_cap || (!DIRECT && n / 255u + 20u > a.out_cap)) {
 		if (lane == 0)
 			lz4e_atomic_or(a.faults, LZ4E_FAULT_RANGE);
 		goto done;

@@ -129,6 +129,28 @@ def test_limited_output(ctx, ref_lib):
         assert (rets[0::5] == sizes).all() and (rets[1::5] == 0).all()
 
 
+def test_runs_longer_than_the_window(ctx, ref_lib):
+    """Blocks above 64 KiB whose length runs alone exceed the 1 KiB staging window (one length
+    byte per 255 bytes, lz4e_compress.c:365-377, :432-446, :511-522): 1 MiB of noise (last
+    literals, 4112 length bytes), 1 MiB of zeros (one match), 700 KB of noise in front of text
+    (literal run inside the loop), next to ordinary blocks in the same launch whose shared
+    memory such a run must not touch."""
+    noise = np.concatenate([common.synth(65536, 1, 900 + b) for b in range(16)])
+    mixed = np.concatenate([noise[:700000], np.tile(common.lcg_text(3000), 120)])[:1048576]
+    tail = np.concatenate([noise[:300000], np.zeros(748576, np.uint8)])
+    datas = [noise, np.zeros(1048576, np.uint8), mixed, tail] + \
+            [common.synth(65536, b & 3, 50 + b) for b in range(12)]
+    specs = [sg.segs_pages(1048576), sg.segs_single(1048576), sg.segs_odd(1048576, 40, 3),
+             sg.segs_single(1048576)] + [sg.segs_odd(65536, 16, b) for b in range(12)]
+    dspecs = [sg.segs_odd(sg.compress_bound(len(d)), 9, 3 + i) for i, d in enumerate(datas)]
+    src, dst, rets = _check_compress(ctx, ref_lib, datas, specs, dspecs)
+    out = common.build_layout(_arena(ctx), [sg.segs_odd(len(d), 7, i) for i, d in enumerate(datas)])
+    r2 = common.gpu_decompress(ctx, dst, rets, out)
+    for b, d in enumerate(datas):
+        assert r2[b] == len(d)
+        assert np.array_equal(out.read_block(b), d)
+
+
 def test_too_many_bvecs(ctx, ref_lib):
     d = common.synth(300, 0, 1)
     spec257 = {"size": 257, "segs": [(i % 4000, 1) for i in range(257)], "skip": 0, "gap": 0}

@@ -94,6 +94,34 @@ def test_compress_body_limited_output(simt, ref_lib, out_cap, sg_dst):
             assert int((got != want).sum()) <= 1, b
 
 
+def test_compress_body_long_length_runs(simt, ref_lib):
+    """Length runs of hundreds of bytes (one length byte per 255 bytes of a literal run or a
+    match): last literals of an incompressible 64 KiB block, a long literal run inside the loop,
+    a 64 KiB match — into linear and scattered destinations through the 1 KiB window.  A window
+    that could not hold such a run by itself is refused (fault flag), never overrun: the launch
+    sizes it from the largest block (lz4e_b200_compress_dev)."""
+    rnd = common.synth(65536, 1, 5)
+    inloop = np.concatenate([rnd[:40000], np.tile(common.lcg_text(500), 60)])[:65536]
+    zeros = np.zeros(65536, np.uint8)
+    both = np.concatenate([rnd[:33000], np.zeros(32536, np.uint8)])
+    datas = [rnd, inloop, zeros, both] * 2
+    specs = [sg.segs_single(65536)] * 4 + [sg.segs_odd(65536, 16, i) for i in range(4)]
+    dspecs = [sg.segs_single(sg.compress_bound(65536))] * 4 + \
+             [sg.segs_odd(sg.compress_bound(65536), 7, i) for i in range(4)]
+    src = _host_layout(specs, datas)
+    dst = _host_layout(dspecs)
+    dst.arena.mem[:] = 0xEE
+    rets, ends, faults = emu.compress(simt, src, dst, in_cap=65536, out_cap=1024)
+    ref_dst, (ref_rets, _) = common.oracle_compress(ref_lib, src, dspecs)
+    assert faults == 0
+    assert np.array_equal(rets, ref_rets)
+    for b in range(len(datas)):
+        assert np.array_equal(dst.read_block(b, rets[b]), ref_dst.read_block(b, ref_rets[b])), b
+    assert np.array_equal(dst.arena.mem, ref_dst.arena.mem[:len(dst.arena.mem)])
+    rets, _, faults = emu.compress(simt, src, dst, in_cap=65536, out_cap=256)
+    assert faults == 1 and (rets == 0).all()
+
+
 @pytest.mark.parametrize("out_cap", [1024, 4352, 64])
 def test_compress_body_packed_table(simt, ref_lib, out_cap):
     """Blocks of at most 4 KiB with the packed 12-bit table (12 KiB for the 8192 byU16 entries):
