@@ -430,7 +430,10 @@ def run_replay(device=0, seed=1):
     try:
         if not os.path.exists(exe):
             subprocess.run(["make", "-C", os.path.dirname(exe)], check=True, capture_output=True)
-        cmd = [exe, "--arena-bios", "--batches", "48", "--device", str(device), "--seed", str(seed)]
+        # two warm-up batches (run and checked like the others, not timed): the first batch on a
+        # fresh context pays its pinned staging, pool and kernel-attribute set-up (about 100 ms)
+        cmd = [exe, "--arena-bios", "--batches", "48", "--warmup", "2", "--device", str(device),
+               "--seed", str(seed)]
         for so in (os.path.join(ROOT, "oracle", "_ref", "liblz4e_ref.so"),
                    os.path.join(ROOT, "oracle", "_build", "liblz4e_port.so")):
             if os.path.exists(so):

@@ -38,6 +38,7 @@ struct opts {
 	int arena_bios, json;
 	unsigned devices; /* > 1: one submitter thread per GPU 0 .. devices-1 in this process */
 	const char *oracle;
+	unsigned warmup; /* batches run and checked before the timed ones, not counted */
 };
 
 static __thread uint32_t rng_state; /* one request stream per submitter thread */
@@ -114,7 +115,7 @@ typedef int (*ref_compress_fn)(const struct bio_vec *, struct bio_vec *, struct 
 
 static void usage(void)
 {
-	puts("lz4e_replay [--qd 256] [--batches 64] [--min-kib 4] [--max-kib 128]\n"
+	puts("lz4e_replay [--qd 256] [--batches 64] [--warmup 0] [--min-kib 4] [--max-kib 128]\n"
 	     "            [--read-pct 30] [--capacity-mib 1024] [--seed 1] [--device 0]\n"
 	     "            [--devices N] [--arena-bios] [--oracle liblz4e_ref.so] [--json]");
 }
@@ -140,6 +141,8 @@ static int parse(int argc, char **argv, struct opts *o)
 			o->qd = (unsigned)atoi(v), i++;
 		} else if (!strcmp(a, "--batches")) {
 			o->batches = (unsigned)atoi(v), i++;
+		} else if (!strcmp(a, "--warmup")) {
+			o->warmup = (unsigned)atoi(v), i++;
 		} else if (!strcmp(a, "--min-kib")) {
 			o->min_kib = (unsigned)atoi(v), i++;
 		} else if (!strcmp(a, "--max-kib")) {
@@ -186,6 +189,7 @@ static int run(struct opts o, struct result *res)
 	uint8_t *shadow, *pages_mem = NULL;
 	double *lat, t_all = 0.0;
 	uint64_t capacity, wbytes = 0, rbytes = 0, wreqs = 0, rreqs = 0, wvecs = 0, rvecs = 0;
+	uint64_t timed_w = 0, timed_r = 0; /* bytes of the timed batches */
 	uint64_t oracle_bytes = 0, oracle_digest = 0, launches0;
 	unsigned int max_pages, b, i, bad = 0, failed = 0;
 	ref_compress_fn ref_compress = NULL;
@@ -251,8 +255,9 @@ static int run(struct opts o, struct result *res)
 	}
 	launches0 = lz4e_b200_kernel_launches(ctx);
 
-	for (b = 0; b < o.batches; b++) {
+	for (b = 0; b < o.warmup + o.batches; b++) {
 		size_t nw = 0, nr = 0, k;
+		const int timed = b >= o.warmup;
 		double t0;
 
 		/* ---- fill the queue ---- */
@@ -271,6 +276,8 @@ static int run(struct opts o, struct result *res)
 				memset(s->pages, 0xA5, bytes);
 				rb[nr++] = &s->bio;
 				rbytes += bytes, rreqs++, rvecs += s->bio.bi_vcnt;
+				if (timed)
+					timed_r += bytes;
 			} else {
 				unsigned int off;
 
@@ -286,6 +293,8 @@ static int run(struct opts o, struct result *res)
 				}
 				wb[nw++] = &s->bio;
 				wbytes += bytes, wreqs++, wvecs += s->bio.bi_vcnt;
+				if (timed)
+					timed_w += bytes;
 				if (ref_compress) {
 					/* the reference on the same bio, into scratch pages */
 					const unsigned int cap = LZ4E_COMPRESSBOUND(bytes);
@@ -308,8 +317,10 @@ static int run(struct opts o, struct result *res)
 		t0 = now_ms();
 		lz4e_dev_submit_writes(dev, wb, nw, wst);
 		lz4e_dev_submit_reads(dev, rb, nr, rst);
-		lat[b] = now_ms() - t0;
-		t_all += lat[b];
+		if (timed) {
+			lat[b - o.warmup] = now_ms() - t0;
+			t_all += lat[b - o.warmup];
+		}
 		/* ---- check ---- */
 		for (k = 0; k < nw; k++) {
 			const struct bio *w = wb[k];
@@ -360,8 +371,8 @@ static int run(struct opts o, struct result *res)
 		bad++;
 	}
 	qsort(lat, o.batches, sizeof(*lat), cmp_double);
-	res->gbs = (double)(wbytes + rbytes) / (t_all * 1e-3) / 1e9;
-	res->wgbs = (double)wbytes / (t_all * 1e-3) / 1e9;
+	res->gbs = (double)(timed_w + timed_r) / (t_all * 1e-3) / 1e9;
+	res->wgbs = (double)timed_w / (t_all * 1e-3) / 1e9;
 	res->p50 = pct(lat, o.batches, 0.50);
 	res->p99 = pct(lat, o.batches, 0.99);
 	res->pmax = lat[o.batches - 1];
@@ -461,7 +472,8 @@ int main(int argc, char **argv)
 	       "\"read_reqs\": %llu, \"write_bytes\": %llu, \"read_bytes\": %llu, "
 	       "\"compressed_bytes\": %llu, \"oracle_compressed_bytes\": %llu, "
 	       "\"per_bio_digest_equal\": %s, \"failed\": %u, \"mismatches\": %u, "
-	       "\"gpu_launches\": %llu, \"submitters\": %u, \"wall_ms\": %.1f}\n",
+	       "\"gpu_launches\": %llu, \"submitters\": %u, \"wall_ms\": %.1f, "
+	       "\"warmup_batches\": %u}\n",
 	       o.qd, o.batches, o.min_kib, o.max_kib, o.read_pct,
 	       o.arena_bios ? "arena (pinned, mirrored)" : "pageable (bounced)",
 	       n > 1 ? ", one submitter thread per GPU in one process" : "", t.gbs, t.wgbs, t.p50,
@@ -469,6 +481,6 @@ int main(int argc, char **argv)
 	       (unsigned long long)t.wbytes, (unsigned long long)t.rbytes,
 	       (unsigned long long)t.cbytes, (unsigned long long)t.obytes,
 	       t.digest < 0 ? "null" : t.digest ? "true" : "false", t.failed, t.bad,
-	       (unsigned long long)t.launches, n, wall);
+	       (unsigned long long)t.launches, n, wall, o.warmup);
 	return t.rc;
 }
