@@ -22,9 +22,22 @@ __global__ void __launch_bounds__(LZ4E_C_MAX_WARPS * 32)
 lz4e_compress_kernel(const lz4e_compress_args a)
 {
 	const uint32_t w = threadIdx.x >> 5;
+	uint32_t lane = threadIdx.x & 31;
 
-	lz4e_compress_warp<DIRECT, GIN, TMA>(a, lz4e_smem + (size_t)w * a.warp_smem,
-					     threadIdx.x & 31, blockIdx.x * a.warps + w);
+	/* opaque to the compiler, which otherwise re-reads SR_TID.X (S2R, ~25
+	 * cycles) in about a hundred places instead of keeping the lane index */
+	asm volatile("" : "+r"(lane));
+	/* the same for this warp's shared-memory base: left to itself the compiler
+	 * rebuilds the address of lz4e_smem (S2R SR_CgaCtaId, MOV, LEA) in front of
+	 * about 75 shared-memory loads, on the encoder's dependent chains */
+	uint32_t soff = (uint32_t)__cvta_generic_to_shared(lz4e_smem) + w * a.warp_smem;
+
+	/* (the 32-bit shared-space address is what is hidden: a pointer that came
+	 * out of an asm statement would lose its "is shared memory" property) */
+	asm volatile("" : "+r"(soff));
+	uint8_t *sm = (uint8_t *)__cvta_shared_to_generic((size_t)soff);
+
+	lz4e_compress_warp<DIRECT, GIN, TMA>(a, sm, lane, blockIdx.x * a.warps + w);
 }
 
 /* ---- K4: decompression, LZ4E_D_WARPS warps per CTA, 32/GS blocks per warp */
@@ -71,14 +84,22 @@ lz4e_decompress_lane_kernel(const lz4e_decompress_args a)
  * 32 sequences per step.  Ten CTAs per SM (what their shared memory allows)
  * instead of the eight that 64 registers gave: 48 registers, one word spilled,
  * 64 KiB blocks over 16 segments 244 -> 253 GB/s ------------------------------ */
+#ifndef LZ4E_W_MINB
 #define LZ4E_W_MINB 10
+#endif
 __global__ void __launch_bounds__(LZ4E_D_WARPS * 32, LZ4E_W_MINB)
 lz4e_decompress_wave_kernel(const lz4e_decompress_args a)
 {
 	__shared__ lz4e_wave_smem sm[LZ4E_D_WARPS];
 	const uint32_t warp = threadIdx.x >> 5;
 
-	lz4e_decompress_wave(a, &sm[warp], blockIdx.x * LZ4E_D_WARPS + warp, threadIdx.x & 31);
+	uint32_t lane = threadIdx.x & 31;
+
+	/* opaque to the compiler: under the 48-register cap it otherwise re-reads
+	 * SR_TID.X (S2R, ~25 cycles) twice per step of the copy loop instead of
+	 * keeping the lane index (253 -> 259 GB/s at 64 KiB x 16 segments) */
+	asm volatile("" : "+r"(lane));
+	lz4e_decompress_wave(a, &sm[warp], blockIdx.x * LZ4E_D_WARPS + warp, lane);
 }
 
 /* ------------------------------------------------------------------------- */
