@@ -89,8 +89,10 @@ const char *lz4e_b200_strerror(lz4e_b200_ctx *ctx);
 /* kernel-selection knobs, the same ones the LZ4E_B200_* environment variables
  * set at context creation (tests and tuning; results never depend on them):
  * "dgroup" lanes per block of the decoder (1, 4, 8, 16; 0 = automatic),
- * "dstage" (-1/0/1), "dvariant" (-1 = automatic), "gin_min", "gin_per_sm",
- * "gin_small".  Returns LZ4E_B200_EINVAL for an unknown key. */
+ * "dstage" (-1/0/1), "dvariant" (-1 = automatic), "dorder", "wave_min",
+ * "wave_serial", "lane_per_sm" (decoders), "gin_min", "gin_per_sm",
+ * "gin_small", "tma", "p12" (compressor).  Returns LZ4E_B200_EINVAL for an
+ * unknown key. */
 int lz4e_b200_ctx_tune(lz4e_b200_ctx *ctx, const char *key, int value);
 int lz4e_b200_ctx_device(lz4e_b200_ctx *ctx);
 int lz4e_b200_ctx_sm_count(lz4e_b200_ctx *ctx);
